@@ -1,0 +1,96 @@
+"""GPU parity, end to end: TS2D(...).predict on a synthetic 3-D study with five random-init group models vs the oracle,
+compared per label NAME (the merged channel order is data dependent), plus the model-level apply() contract."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import pipeline as opipe
+from tests.conftest import GOLDEN, synthetic_ct
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def zoo(tmp_path_factory):
+    from totalsegmentator2d_b200 import synth
+    root = str(tmp_path_factory.mktemp("models"))
+    arch = synth.make_arch_kwargs([32, 64, 128])
+    groups = {g: labels[:4 + i] for i, (g, labels) in enumerate(synth.TS2D_V2_GROUPS.items())}
+    synth.write_model_zoo(root, "ts2d-v2-ep4000b2", arch, (64, 64), (1.5, 1.5), groups, base_seed=300)
+    return root, groups
+
+
+def _oracle_models(root, groups):
+    return {f"ts2d-v2-ep4000b2_{g}": opipe.OracleModel(opipe.find_training_dir(os.path.join(root, f"ts2d-v2-ep4000b2_{g}", "r001"))) for g in groups}
+
+
+@pytest.mark.parametrize("precision", ["fp32", "fp16"])
+def test_predict_3d_study_matches_oracle(zoo, precision):
+    from totalsegmentator2d_b200.core.util.meta import get_annotation_labels
+    from totalsegmentator2d_b200.image import Image
+    from totalsegmentator2d_b200.tool import TS2D
+    root, groups = zoo
+    vol = synthetic_ct((150, 30, 100), seed=20260000)
+    d = np.diag([-1.0, -1.0, 1.0])
+    img = Image(vol, (1.5, 1.5, 1.5), (1.0, 2.0, 3.0), d.reshape(-1))
+    with TS2D(key="ts2d", models_root=root, param={"b200.precision": precision}) as ts:
+        assert sorted(ts.models) == [f"ts2d-v2-ep4000b2_{g}" for g in sorted(groups)]
+        res = ts.predict(img)
+        seg = res.get_segmentation()
+        assert seg.GetSize() == (100, 1, 150) and seg.GetNumberOfComponentsPerPixel() == sum(len(v) for v in groups.values())
+        merged = np.asarray(seg.array).reshape(150, 100, -1)
+        info = get_annotation_labels(seg, fetch=False)
+        per_model = {m: np.asarray(res.get_segmentation(m).array).reshape(150, 100, -1) for m in res.models}
+        projs = {k: np.asarray(v.array).reshape(150, 100) for k, v in res.get_projection().items()}
+    ref = opipe.predict_study(vol, (1.5, 1.5, 1.5), d, _oracle_models(root, groups), mode="ideal")
+    assert np.array_equal(projs["max"], ref["projections"]["max"]) and np.array_equal(projs["mean"], ref["projections"]["mean"])
+    assert [v["name"] for v in sorted(info.values(), key=lambda v: v["value"])] == ref["names"], "merged channel order (present first) differs"
+    agree = np.mean([np.mean(merged[..., info[n]["value"] - 1] == ref["segmentation"][..., i]) for i, n in enumerate(ref["names"])])
+    print(f"{precision}: merged mask agreement {agree:.5f}")
+    assert agree >= 0.999
+    for mid, arr in per_model.items():
+        assert np.mean(arr == ref["models"][mid]) >= 0.999
+
+
+def test_predict_2d_inputs_and_apply_contract(zoo):
+    from totalsegmentator2d_b200 import nrrd
+    from totalsegmentator2d_b200.image import Image
+    from totalsegmentator2d_b200.tool import TS2D
+    root, groups = zoo
+    img = nrrd.read_nrrd(os.path.join(GOLDEN, "sample_s0332.nrrd"))         # (X,1,Z) container, 2 channels: the pre-projected path
+    with TS2D(key="ts2d_cardiac", models_root=root, param={"b200.precision": "fp32"}) as ts:
+        assert list(ts.models) == ["ts2d-v2-ep4000b2_cardiac"]
+        res = ts.predict(img)
+        seg = res.get_segmentation()
+        assert seg.GetSize() == (269, 1, 505) and set(res.get_projection()) == {"ch0", "ch1"}
+        om = _oracle_models(root, {"cardiac": None})["ts2d-v2-ep4000b2_cardiac"]
+        chw = np.moveaxis(np.asarray(img.array)[:, 0], -1, 0)
+        ref = opipe.predict_model(chw, (1.5, 1.5), om, mode="ideal")
+        assert np.mean(np.asarray(seg.array)[:, 0] == ref) >= 0.999
+        model = ts.models["ts2d-v2-ep4000b2_cardiac"]
+        one = Image(np.asarray(img.array)[:, 0], (1.5, 1.5), (0, 0), None, is_vector=True)
+        out = model.apply([one, one])
+        assert set(out) == {"image1", "image2"} and np.array_equal(out["image1"].array, out["image2"].array)
+        with pytest.raises(RuntimeError):
+            model.apply([one, os.path.join(GOLDEN, "sample_s0332.nrrd")])
+        with pytest.raises(RuntimeError):
+            ts.predict(Image(np.zeros((8, 8), np.float32)))                  # 1 channel into a 2-channel model
+
+
+def test_save_writes_reference_file_names(zoo, tmp_path):
+    from totalsegmentator2d_b200 import nrrd
+    from totalsegmentator2d_b200.main import ts2d_run
+    root, groups = zoo
+    os.environ["TS2D_MODELS"] = root
+    try:
+        ts2d_run(os.path.join(GOLDEN, "sample_s0521.nrrd"), str(tmp_path), model="ts2d-v2-ep4000b2", visualize=True, save_all=True, silent=True)
+    finally:
+        os.environ.pop("TS2D_MODELS")
+    s = "sample_s0521"
+    expect = [f"{s}.seg.nrrd", f"{s}.seg.png", f"{s}_max.nrrd", f"{s}_mean.nrrd"] + [f"{s}-{g}.seg.{e}" for g in groups for e in ("nrrd", "png")]
+    for fn in expect:                                  # reference test/test_030_cli.py:46-49
+        assert os.path.exists(os.path.join(str(tmp_path), fn)), fn
+    seg = nrrd.read_nrrd(os.path.join(str(tmp_path), f"{s}.seg.nrrd"))
+    assert seg.GetSize() == (53, 1, 133) and seg.HasMetaDataKey("Segment0_Name") and seg.GetMetaData("Segment0_LabelValue") == "1"

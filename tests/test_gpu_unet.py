@@ -1,0 +1,113 @@
+"""GPU parity: the U-Net engine vs the oracle's torch-CPU PlainConvUNet (fp32 CUDA-core path <= 1e-4; bf16/fp16
+tcgen05 path <= the stated mixed-precision tolerance), layer by layer and end to end through blend/export."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import nnunet_inf, nnunet_net
+
+pytestmark = pytest.mark.gpu
+
+
+def _make(features, patch, heads=5, in_ch=2, precision="fp32", tc=True, seed=3, strides=None, mirror=True, n_conv=2):
+    from totalsegmentator2d_b200 import synth
+    from totalsegmentator2d_b200.core.inference.predictor import B200nnUNetPredictor
+    arch = synth.make_arch_kwargs(features, strides, n_conv, n_conv)
+    labels = [f"l{i}" for i in range(heads)]
+    plans = synth.make_plans(arch, patch, (1.5, 1.5), ["ZScoreNormalization"] * in_ch)
+    dj = synth.make_dataset_json([f"c{i}" for i in range(in_ch)], labels)
+    sd = synth.init_state_dict(arch, in_ch, heads, seed, with_aliases=True)
+    p = B200nnUNetPredictor(use_mirroring=mirror, precision=precision, use_tensor_cores=tc, max_batch=4)
+    p.manual_initialization(plans, "2d", dj, [sd], (0, 1))
+    spec = nnunet_net.ArchSpec(arch, in_ch, heads)
+    return p, sd, spec
+
+
+def _tiles(n, c, patch, seed, dtype):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(n, c, *patch, generator=g)
+    return x, x.permute(0, 2, 3, 1).contiguous().to(dtype).cuda()
+
+
+@pytest.mark.parametrize("features,patch,strides", [([8, 16, 32], (32, 48), None), ([4, 8], (16, 16), None),
+                                                     ([8, 16, 16], (24, 40), [[1, 1], [2, 2], [2, 1]])])
+def test_fp32_direct_path_logits(features, patch, strides):
+    p, sd, spec = _make(features, patch, precision="fp32", strides=strides)
+    x, xd = _tiles(3, 2, patch, 1, torch.float32)
+    got = p.predict_tile_logits(xd).cpu()
+    with torch.no_grad():
+        ref = nnunet_net.unet_forward(x, sd, spec)
+    assert float((got - ref).abs().max()) <= 1e-4, float((got - ref).abs().max())
+
+
+def _layer_errors(p, sd, spec, x, xd):
+    coll = {}
+    with torch.no_grad():
+        nnunet_net.unet_forward(x, sd, spec, collect=coll)
+    errs = {}
+    for name, ref in coll.items():
+        got = p.forward_debug(xd, name, tuple(ref.shape[1:])).cpu()
+        errs[name] = float((got - ref).abs().max())
+    return errs
+
+
+@pytest.mark.parametrize("precision,tol", [("bf16", 0.12), ("fp16", 0.02)])
+def test_tensor_core_layers(precision, tol):
+    """every conv layer of a TC-eligible net (KC=32 and 64, stride-2 parity maps, several BN) against the fp32 oracle.
+    Activations are O(1) after InstanceNorm; bf16 has 8 mantissa bits (2^-9 = 2e-3 per rounding), fp16 11 bits."""
+    dt = torch.bfloat16 if precision == "bf16" else torch.float16
+    p, sd, spec = _make([32, 64, 128, 256], (64, 64), heads=7, precision=precision, seed=5)
+    x, xd = _tiles(4, 2, (64, 64), 2, dt)
+    x = xd.float().cpu().permute(0, 3, 1, 2).contiguous()      # the oracle sees the rounded input
+    errs = _layer_errors(p, sd, spec, x, xd)
+    print(precision, {k: round(v, 4) for k, v in errs.items()})
+    assert max(errs.values()) <= tol, errs
+
+
+def test_tensor_core_equals_direct_same_precision():
+    """tcgen05 path vs CUDA-core path at the same storage precision: only fp32 accumulation order differs"""
+    pt, sd, spec = _make([32, 64, 128], (64, 96), heads=6, precision="fp16", tc=True, seed=8)
+    pd, _, _ = _make([32, 64, 128], (64, 96), heads=6, precision="fp16", tc=False, seed=8)
+    x, xd = _tiles(3, 2, (64, 96), 4, torch.float16)
+    a = pt.predict_tile_logits(xd).cpu()
+    b = pd.predict_tile_logits(xd).cpu()
+    assert float((a - b).abs().max()) <= 2e-2, float((a - b).abs().max())
+
+
+def test_tensor_core_ragged_tiles_and_small_levels():
+    """W=160/80/40/20 (tiles overhang the image), deepest level 5x3.. covers masked rows and multi-image tiles"""
+    p, sd, spec = _make([32, 32, 64, 64, 64], (48, 160), heads=4, precision="fp16", seed=9)
+    x, xd = _tiles(3, 2, (48, 160), 6, torch.float16)
+    x = xd.float().cpu().permute(0, 3, 1, 2).contiguous()
+    errs = _layer_errors(p, sd, spec, x, xd)
+    assert max(errs.values()) <= 0.03, errs
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-4), ("fp16", 2e-2), ("bf16", 1.5e-1)])
+@pytest.mark.parametrize("mirror", [False, True])
+def test_sliding_window_logits_and_mask(precision, tol, mirror):
+    """predict_logits_from_preprocessed_data (tiling + mirror TTA + Gaussian blend + head) vs the oracle, and the
+    thresholded masks: >= 99.9% agreement for fp32/fp16, reported for bf16."""
+    feats = [32, 64, 128] if precision != "fp32" else [8, 16, 32]
+    p, sd, spec = _make(feats, (64, 64), heads=6, precision=precision, seed=11, mirror=mirror)
+    g = torch.Generator().manual_seed(13)
+    data = torch.randn(2, 1, 150, 100, generator=g)
+    got = p.predict_logits_from_preprocessed_data(data).cpu()
+    net = lambda t: nnunet_net.unet_forward(t, sd, spec)
+    with torch.no_grad():
+        ref = nnunet_inf.predict_sliding_window(net, data, (64, 64), 6, 0.5, (0, 1) if mirror else None, True, "ideal")
+    err = float((got - ref).abs().max())
+    agree = float(((got > 0) == (ref > 0)).float().mean())
+    print(f"{precision} mirror={mirror}: max |dlogit| {err:.4g}, mask agreement {agree:.5f}")
+    assert got.shape == ref.shape and err <= tol
+    if precision != "bf16":
+        assert agree >= 0.999
+
+
+def test_errors_are_loud():
+    from totalsegmentator2d_b200 import _lib as L
+    p, sd, spec = _make([8, 16], (16, 16))
+    with pytest.raises(L.TS2DError):
+        p.predict_logits_from_preprocessed_data(torch.zeros(2, 16, 16))
+    with pytest.raises(L.TS2DError):
+        _make([8, 16], (18, 18))                      # patch not divisible by the strides

@@ -1,0 +1,156 @@
+"""CPU suite: pins the oracle against the reference's asset files and against the scipy/torch primitives that
+upstream nnU-Net itself calls.  (The reference's own tests hold no numeric vectors: parity is otherwise unpinned.)"""
+import ctypes
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import geometry, nnunet_inf, nnunet_net, nnunet_pre, pipeline
+from totalsegmentator2d_b200 import nrrd, synth
+from tests.conftest import GOLDEN, ROOT, synthetic_ct
+
+
+def _read(name):
+    return nrrd.read_nrrd(os.path.join(GOLDEN, name))
+
+
+def test_asset_s0616_is_reference_projection_output():
+    """sample_s0616 is a real output of the reference's projection stage: ch1 integral (max), ch0 = k/261 in
+    double (mean = double sum / N), max >= mean -> channel order {0: mean, 1: max} and double accumulation."""
+    img = _read("sample_s0616.nrrd")
+    a = np.asarray(img.array)
+    assert a.dtype == np.float64 and a.shape == (644, 337, 2)
+    mean, mx = a[..., 0], a[..., 1]
+    assert np.all(mx == np.round(mx))
+    assert np.all(mx >= mean)
+    k = mean * 261.0
+    assert np.max(np.abs(k - np.round(k))) < 1e-9          # exact multiples of 1/261 in double
+    assert np.abs(mean - np.round(mean)).max() > 0.1        # and genuinely fractional
+
+
+def test_asset_s0332_geometry_of_project():
+    """sample_s0332 carries project()'s output geometry: size (X,1,Z), spacing_y = Ny*sy (403.5 = 269*1.5), RAI."""
+    img = _read("sample_s0332.nrrd")
+    assert img.GetSize() == (269, 1, 505) and img.GetNumberOfComponentsPerPixel() == 2
+    assert img.GetSpacing() == (1.5, 403.5, 1.5)
+    assert np.allclose(img.direction_matrix(), -np.eye(3))
+    a = np.asarray(img.array)
+    assert np.all(a[..., 1] == np.round(a[..., 1])) and np.all(a[..., 1] >= a[..., 0])
+    size, spacing, origin, d = geometry.projected_geometry((269, 269, 505), (1.5, 1.5, 1.5), (0, 0, 0), -np.eye(3), 1)
+    assert size == [269, 1, 505] and spacing == [1.5, 403.5, 1.5]
+
+
+def test_orientation_remap_s0521():
+    img = _read("sample_s0521.nrrd")
+    perm, flip = geometry.orientation_remap(img.direction_matrix(), "RAI")
+    assert perm == (0, 1, 2) and flip == (False, False, True)          # RAS-like asset: only z flips
+    # permuted / oblique
+    d = np.array([[0.0, 0.0, 1.0], [0.98, -0.2, 0.0], [0.2, 0.98, 0.0]])      # axis0->P, axis1->S(ish), axis2->L
+    perm, flip = geometry.orientation_remap(d, "RAI")
+    assert perm == (2, 0, 1) and flip == (True, True, True)
+    vol = np.arange(2 * 3 * 4).reshape(2, 3, 4).astype(np.int16)
+    out = geometry.reorient_array(vol, perm, flip)
+    assert out.shape == (3, 4, 2)[::-1][::-1] or out.size == vol.size
+
+
+def test_projection_known_answer_s0521():
+    """freeze the oracle projection of the only 3-D asset (known-answer test)."""
+    img = _read("sample_s0521.nrrd")
+    perm, flip = geometry.orientation_remap(img.direction_matrix(), "RAI")
+    rai = geometry.reorient_array(np.asarray(img.array), perm, flip)
+    proj = geometry.project_channels(rai, ["mean", "max"])
+    assert proj.shape == (2, 133, 53) and proj.dtype == np.float32
+    with open(os.path.join(GOLDEN, "s0521_projection.json")) as f:
+        gold = json.load(f)
+    assert hashlib.sha256(proj[0].tobytes()).hexdigest() == gold["mean_sha256"]
+    assert hashlib.sha256(proj[1].tobytes()).hexdigest() == gold["max_sha256"]
+    # the C restatement agrees bit for bit
+    lib = ctypes.CDLL(os.path.join(ROOT, "oracle", "liboracle_projection.so"))
+    out = np.empty((133, 53), dtype=np.float32)
+    for fn, ref in (("oracle_project_mean_i16", proj[0]), ("oracle_project_max_i16", proj[1])):
+        getattr(lib, fn)(rai.ctypes.data_as(ctypes.c_void_p), ctypes.c_int64(133), ctypes.c_int64(120), ctypes.c_int64(53),
+                         out.ctypes.data_as(ctypes.c_void_p))
+        assert np.array_equal(out, ref)
+
+
+def test_crop_normalize_resample_against_primitives():
+    rng = np.random.default_rng(3)
+    data = rng.normal(size=(2, 1, 40, 30)).astype(np.float32)
+    data[:, :, :5] = 0
+    data[:, :, :, 27:] = 0
+    out, props = nnunet_pre.run_case_npy(data, [1498.5, 1.5, 1.5], [1.5, 1.5], ["ZScoreNormalization", "CTNormalization"],
+                                         {"1": {"percentile_00_5": -1.0, "percentile_99_5": 1.2, "mean": 0.1, "std": 0.8}})
+    assert props["bbox_used_for_cropping"] == [[0, 1], [5, 40], [0, 27]]
+    assert out.shape == (2, 1, 35, 27)
+    assert abs(out[0].mean()) < 1e-5 and abs(out[0].std() - 1) < 1e-5
+    c = np.clip(data[1, :, 5:, :27], -1.0, 1.2)
+    assert np.allclose(out[1], (c - 0.1) / 0.8, atol=1e-6)
+    # resampling active: 0.75 mm data on a 1.5 mm plan halves the grid
+    out2, _ = nnunet_pre.run_case_npy(data, [749.25, 0.75, 0.75], [1.5, 1.5], ["NoNormalization"] * 2)
+    assert out2.shape == (2, 1, 18, 14)
+
+
+def test_sliding_window_layout_matches_survey():
+    assert nnunet_inf.compute_steps_for_sliding_window((1000, 512), (512, 512), 0.5) == [[0, 244, 488], [0]]
+    assert len(nnunet_inf.compute_steps_for_sliding_window((2000, 512), (512, 512), 0.5)[0]) == 7
+    g = nnunet_inf.compute_gaussian((64, 64))
+    assert g.dtype == torch.float16 and float(g.max()) == 10.0 and float(g.min()) > 0
+
+
+def test_unet_oracle_equals_torch_modules():
+    """the functional oracle forward == an nn.Module PlainConvUNet assembled from torch layers with the same weights"""
+    arch = synth.make_arch_kwargs([4, 8, 16])
+    sd = synth.init_state_dict(arch, 2, 3, seed=1)
+    spec = nnunet_net.ArchSpec(arch, 2, 3)
+    x = torch.randn(2, 2, 16, 24, generator=torch.Generator().manual_seed(0))
+    y = nnunet_net.unet_forward(x, sd, spec)
+    assert y.shape == (2, 3, 16, 24)
+    import torch.nn as nn
+
+    def block(cin, cout, stride, p):
+        m = nn.Sequential(nn.Conv2d(cin, cout, 3, stride, 1), nn.InstanceNorm2d(cout, eps=1e-5, affine=True), nn.LeakyReLU(0.01))
+        m[0].weight.data, m[0].bias.data = sd[p + ".conv.weight"], sd[p + ".conv.bias"]
+        m[1].weight.data, m[1].bias.data = sd[p + ".norm.weight"], sd[p + ".norm.bias"]
+        return m
+    skips, cur, cin = [], x, 2
+    for s, f in enumerate([4, 8, 16]):
+        for i in range(2):
+            cur = block(cin, f, (1 if s == 0 else 2) if i == 0 else 1, f"encoder.stages.{s}.0.convs.{i}")(cur)
+            cin = f
+        skips.append(cur)
+    for d in range(2):
+        up = nn.ConvTranspose2d(skips[-(d + 1)].shape[1] if d == 0 else cur.shape[1], skips[-(d + 2)].shape[1], 2, 2)
+        up.weight.data, up.bias.data = sd[f"decoder.transpconvs.{d}.weight"], sd[f"decoder.transpconvs.{d}.bias"]
+        cur = torch.cat((up(cur if d else skips[-1]), skips[-(d + 2)]), 1)
+        f = skips[-(d + 2)].shape[1]
+        for i in range(2):
+            cur = block(cur.shape[1], f, 1, f"decoder.stages.{d}.convs.{i}")(cur)
+    head = nn.Conv2d(4, 3, 1)
+    head.weight.data, head.bias.data = sd["decoder.seg_layers.1.weight"], sd["decoder.seg_layers.1.bias"]
+    with torch.no_grad():
+        assert torch.allclose(head(cur), y, atol=1e-5)
+    assert nnunet_net.conv_flops(nnunet_net.ArchSpec(synth.cs512_arch(), 2, 26), 512, 512) == pytest.approx(119.7e9, rel=2e-3)
+
+
+def test_mirror_and_blend_properties():
+    """a flip-equivariant 'network' must be unchanged by mirror TTA; blending a constant gives the constant"""
+    net = lambda x: x[:, :1] * 2.0 + 1.0
+    x = torch.randn(1, 1, 70, 50, generator=torch.Generator().manual_seed(2))
+    lg = nnunet_inf.predict_sliding_window(net, x.permute(1, 0, 2, 3), (32, 32), 1, 0.5, (0, 1), True, "ideal")
+    assert torch.allclose(lg[0, 0], x[0, 0] * 2 + 1, atol=1e-5)
+    lg16 = nnunet_inf.predict_sliding_window(net, x.permute(1, 0, 2, 3), (32, 32), 1, 0.5, (0, 1), True, "faithful")
+    # upstream keeps fp16 accumulators and an fp16 Gaussian: near tile corners (tiny weights) that costs ~2e-2
+    assert torch.allclose(lg16, lg, atol=6e-2) and float((lg16 - lg).abs().mean()) < 3e-3
+
+
+def test_combine_order_is_present_first():
+    a = np.zeros((4, 4, 3), np.uint8)
+    a[0, 0, 2] = 1
+    b = np.zeros((4, 4, 2), np.uint8)
+    b[1, 1, 0] = 1
+    merged, names = pipeline.combine_segmentations([a, b], [["x", "y", "z"], ["p", "q"]])
+    assert names == ["z", "x", "y", "p", "q"] and merged.shape == (4, 4, 5) and merged[0, 0, 0] == 1

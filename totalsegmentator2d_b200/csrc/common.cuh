@@ -1,0 +1,75 @@
+// Shared helpers for libts2d_b200 (sm_100a only).
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <atomic>
+#include <string>
+
+#include "../../include/ts2d_b200.h"
+
+namespace ts2d {
+
+void set_error(const char *fmt, ...);
+extern std::atomic<long long> g_launches;
+
+#define TS2D_CHECK_CUDA(expr)                                                                         \
+    do {                                                                                              \
+        cudaError_t _e = (expr);                                                                      \
+        if (_e != cudaSuccess) {                                                                      \
+            ::ts2d::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+            return TS2D_ERR_CUDA;                                                                     \
+        }                                                                                             \
+    } while (0)
+
+#define TS2D_REQUIRE(cond, ...)             \
+    do {                                    \
+        if (!(cond)) {                      \
+            ::ts2d::set_error(__VA_ARGS__); \
+            return TS2D_ERR_ARG;            \
+        }                                   \
+    } while (0)
+
+#define TS2D_LAUNCH_CHECK()                                                                  \
+    do {                                                                                     \
+        cudaError_t _e = cudaGetLastError();                                                 \
+        if (_e != cudaSuccess) {                                                             \
+            ::ts2d::set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), __FILE__, __LINE__); \
+            return TS2D_ERR_CUDA;                                                            \
+        }                                                                                    \
+        ::ts2d::g_launches.fetch_add(1, std::memory_order_relaxed);                          \
+    } while (0)
+
+static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+constexpr int kNumSMs = 148;   // B200
+
+// activation element <-> float
+template <typename T> __device__ __forceinline__ float to_f32(T v);
+template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <> __device__ __forceinline__ float to_f32<__half>(__half v) { return __half2float(v); }
+template <typename T> __device__ __forceinline__ T from_f32(float v);
+template <> __device__ __forceinline__ float from_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+template <> __device__ __forceinline__ __half from_f32<__half>(float v) { return __float2half_rn(v); }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+static inline size_t prec_size(int precision) { return precision == TS2D_PREC_F32 ? 4 : 2; }
+
+}  // namespace ts2d

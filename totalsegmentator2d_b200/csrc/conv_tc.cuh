@@ -1,0 +1,365 @@
+// K4/K6: implicit-GEMM convolution on the 5th-generation tensor cores (tcgen05 + TMEM), fed by TMA.
+//
+// Replaces the Conv2d / ConvTranspose2d library calls (cuDNN under torch) that the reference reaches through
+// nnUNetPredictor (reference ts2d/core/inference/nnu.py:149-166, prediction_worker.py:209).
+//
+// GEMM view:  D[M = 128 output pixels][N = BN output channels] += A[M][K] * B[N][K],  K = taps * Cin.
+//   A  NHWC activations. One K-chunk = (filter tap, KC input channels). The 128 pixels of a tile are a
+//      (tn images) x (th rows) x (tw cols) box, so a tap is the same box shifted by (r-pad, s-pad): ONE 4-D TMA
+//      box load per K-chunk; TMA zero-fills out-of-bounds coordinates, which *is* the conv zero padding.
+//      Stride-2 convs use a 5-D "parity" view of the same buffer (w = 2*w2 + px folded into the channel axis,
+//      h = 2*h2 + py as its own axis), so every tap is again a dense box.  The box lands in shared memory as
+//      128 rows x KC channels with the 128-byte (KC=64) or 64-byte (KC=32) swizzle = the canonical K-major
+//      UMMA operand layout.
+//   B  weights repacked [tap][Cout][Cin] (K-major), 3-D TMA box (KC, BN, 1).
+//   D  fp32 accumulators in TMEM, double buffered (2 x BN columns): the epilogue of tile i overlaps the MMAs
+//      of tile i+1.
+// Warp roles (192 threads): warp 0 = TMA producer (one lane), warp 1 = TMEM allocator + MMA issuer (one lane),
+// warps 2-5 = epilogue (TMEM lane group = warp % 4): tcgen05.ld -> +bias -> round to bf16/fp16 -> per-channel
+// sum / sum-of-squares of the ROUNDED values for InstanceNorm (warp transpose-reduction, accumulated in registers
+// across the CTA's tiles, flushed with double atomics when the image index changes) -> 16-byte global stores.
+// Persistent grid: one CTA per SM, static round-robin over (m_tile, n_tile) with n fastest so that CTAs running
+// concurrently share the A tile through L2.
+#pragma once
+#include "common.cuh"
+
+namespace ts2d {
+
+struct ConvTcParams {
+    int N, Hout, Wout, Cout;     // GEMM-side output grid (for transposed conv: the INPUT grid)
+    int cin_chunks;              // Cin / KC
+    int taps, kw;                // taps = kh*kw (1 for 1x1 / transposed conv slices)
+    int pad_h, pad_w;
+    int stride2;                 // 0: stride 1 (4-D map), 1: stride (2,2) (5-D parity map)
+    int in_ps;                   // input pixel stride in elements (parity view: px * in_ps selects the odd column)
+    int tw, th, tn;              // tile box: tw*th*tn == 128
+    int tiles_w, tiles_h, tiles_n;
+    int n_tiles_n;               // Cout / BN
+    // output addressing: pixel (n, y*my + dy, x*mx + dx) of an image Hfull x Wfull with pixel stride out_ps elements
+    int my, mx, Hfull, Wfull;
+    long long out_ps;
+    void *out;
+    const float *bias;           // [Cout] or null
+    double *stats;               // [N][Cout][2] or null
+    int tap_base_from_grid_y;    // transposed conv: blockIdx.y selects (dy,dx) = weight slice and output offset
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "@P1 bra DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *tm, uint64_t *bar, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                 ::"r"(smem_u32(dst)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(void *dst, const CUtensorMap *tm, uint64_t *bar, int c0, int c1, int c2, int c3) {
+    asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+                 ::"r"(smem_u32(dst)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+__device__ __forceinline__ void tma_load_5d(void *dst, const CUtensorMap *tm, uint64_t *bar, int c0, int c1, int c2, int c3, int c4) {
+    asm volatile("cp.async.bulk.tensor.5d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
+                 ::"r"(smem_u32(dst)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4) : "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_commit(uint64_t *bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tcgen05_mma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+          "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
+          "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+          "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// K-major shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout), swizzle by row width.
+template <int KC>
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr) {
+    constexpr uint64_t layout = (KC == 64) ? 2ull /*SWIZZLE_128B*/ : 4ull /*SWIZZLE_64B*/;
+    constexpr uint64_t sbo = (KC == 64) ? 1024 : 512;   // bytes between 8-row groups
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+    d |= (uint64_t)1 << 16;                 // LBO (unused for swizzled K-major)
+    d |= (uint64_t)(sbo >> 4) << 32;
+    d |= (uint64_t)1 << 46;                 // descriptor version (sm_100)
+    d |= layout << 61;
+    return d;
+}
+// instruction descriptor: D=F32, A/B = F16(0)/BF16(1), both K-major, N>>3 at [17,23), M>>4 at [24,29)
+template <typename DT>
+__device__ __forceinline__ uint32_t make_idesc(int n) {
+    const uint32_t fmt = sizeof(DT) == 2 && std::is_same<DT, __nv_bfloat16>::value ? 1u : 0u;
+    return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(n >> 3) << 17) | ((128u >> 4) << 24);
+}
+
+template <int BN> struct TcCfg {
+    static constexpr int kTmemCols = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
+};
+template <int BN, int KC> constexpr int tc_stage_bytes() { return (128 + BN) * KC * 2; }
+template <int BN, int KC> constexpr int tc_num_stages() {
+    return (200 * 1024 / tc_stage_bytes<BN, KC>()) > 8 ? 8 : (200 * 1024 / tc_stage_bytes<BN, KC>());
+}
+template <int BN, int KC> constexpr int tc_smem_bytes() { return tc_num_stages<BN, KC>() * tc_stage_bytes<BN, KC>() + 1024 /*align*/ + 256 /*barriers*/; }
+
+template <typename DT> __device__ __forceinline__ uint32_t pack2(float a, float b);
+template <> __device__ __forceinline__ uint32_t pack2<__nv_bfloat16>(float a, float b) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t *>(&v);
+}
+template <> __device__ __forceinline__ uint32_t pack2<__half>(float a, float b) {
+    __half2 v = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t *>(&v);
+}
+template <typename DT> __device__ __forceinline__ float2 unpack2(uint32_t u);
+template <> __device__ __forceinline__ float2 unpack2<__nv_bfloat16>(uint32_t u) { return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162 *>(&u)); }
+template <> __device__ __forceinline__ float2 unpack2<__half>(uint32_t u) { return __half22float2(*reinterpret_cast<__half2 *>(&u)); }
+
+// lane L ends up with the sum over the warp of x[L]; 31 shuffles
+__device__ __forceinline__ float warp_transpose_sum32(float (&x)[32], int lane) {
+#pragma unroll
+    for (int step = 16; step >= 1; step >>= 1) {
+        const bool upper = (lane & step) != 0;
+#pragma unroll
+        for (int i = 0; i < step; ++i) {
+            const float send = upper ? x[i] : x[i + step];
+            const float keep = upper ? x[i + step] : x[i];
+            x[i] = keep + __shfl_xor_sync(0xffffffffu, send, step);
+        }
+    }
+    return x[0];
+}
+
+template <int BN, int KC, typename DT>
+__global__ void __launch_bounds__(192, 1)
+conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const ConvTcParams p) {
+    constexpr int kStages = tc_num_stages<BN, KC>();
+    constexpr int kABytes = 128 * KC * 2;
+    constexpr int kStageBytes = tc_stage_bytes<BN, KC>();
+    constexpr int kTmemCols = TcCfg<BN>::kTmemCols;
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t *full_bar = reinterpret_cast<uint64_t *>(smem + kStages * kStageBytes);
+    uint64_t *empty_bar = full_bar + kStages;
+    uint64_t *tmem_full = empty_bar + kStages;     // [2]
+    uint64_t *tmem_empty = tmem_full + 2;          // [2]
+    uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int tap_base = p.tap_base_from_grid_y ? blockIdx.y : 0;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+        for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], 128); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr)), "n"(kTmemCols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    const int m_tiles = p.tiles_n * p.tiles_h * p.tiles_w;
+    const int total_tiles = m_tiles * p.n_tiles_n;
+    const int k_chunks = p.taps * p.cin_chunks;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                const int mt = tile / p.n_tiles_n, nt = tile % p.n_tiles_n;
+                const int xt = mt % p.tiles_w, yt = (mt / p.tiles_w) % p.tiles_h, nn = mt / (p.tiles_w * p.tiles_h);
+                const int x0 = xt * p.tw, y0 = yt * p.th, n0 = nn * p.tn;
+                for (int kc = 0; kc < k_chunks; ++kc) {
+                    const int tap = kc / p.cin_chunks, cc = kc % p.cin_chunks;
+                    const int r = tap / p.kw, s = tap % p.kw;
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    uint8_t *sa = smem + stage * kStageBytes;
+                    uint8_t *sb = sa + kABytes;
+                    mbar_expect_tx(&full_bar[stage], kStageBytes);
+                    if (!p.stride2) {
+                        tma_load_4d(sa, &tmA, &full_bar[stage], cc * KC, x0 + s - p.pad_w, y0 + r - p.pad_h, n0);
+                    } else {
+                        // input row 2*oy + r - pad = 2*h2 + py ; input col 2*ox + s - pad = 2*w2 + px
+                        const int dr = r - p.pad_h, ds = s - p.pad_w;
+                        const int py = dr & 1, px = ds & 1;
+                        const int hoff = (dr - py) / 2, woff = (ds - px) / 2;
+                        tma_load_5d(sa, &tmA, &full_bar[stage], px * p.in_ps + cc * KC, x0 + woff, py, y0 + hoff, n0);
+                    }
+                    tma_load_3d(sb, &tmB, &full_bar[stage], cc * KC, nt * BN, tap_base + tap);
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc<DT>(BN);
+            int stage = 0;
+            uint32_t phase = 0;
+            int it = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+                const int buf = it & 1;
+                const uint32_t use = (uint32_t)(it >> 1);
+                mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);
+                tcgen05_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(buf * BN);
+                for (int kc = 0; kc < k_chunks; ++kc) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tcgen05_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * kStageBytes);
+                    const uint32_t sb = sa + kABytes;
+                    const uint64_t adesc = make_smem_desc<KC>(sa);
+                    const uint64_t bdesc = make_smem_desc<KC>(sb);
+#pragma unroll
+                    for (int k = 0; k < KC / 16; ++k) {
+                        // advance 16 elements = 32 bytes along K inside the swizzled row: +2 in the (addr>>4) field
+                        tcgen05_mma_f16(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kc | k) ? 1u : 0u);
+                    }
+                    tcgen05_commit(&empty_bar[stage]);       // frees the smem slot once these MMAs retire
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+                tcgen05_commit(&tmem_full[buf]);             // accumulator complete
+            }
+        }
+    } else {
+        // ===================== epilogue (warps 2..5) =====================
+        const int q = warp & 3;                 // TMEM lane group this warp may access
+        const int row = q * 32 + lane;          // accumulator row = pixel index in the tile
+        const int ix = row % p.tw, iy = (row / p.tw) % p.th, in_ = row / (p.tw * p.th);
+        DT *out = reinterpret_cast<DT *>(p.out);
+        const bool do_stats = p.stats != nullptr;
+        const bool fast_stats = do_stats && p.tn == 1;
+        float racc1[BN / 32], racc2[BN / 32];
+#pragma unroll
+        for (int i = 0; i < BN / 32; ++i) { racc1[i] = 0.f; racc2[i] = 0.f; }
+        int cur_n = -1, cur_nt = -1;
+        int it = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+            const int mt = tile / p.n_tiles_n, nt = tile % p.n_tiles_n;
+            const int xt = mt % p.tiles_w, yt = (mt / p.tiles_w) % p.tiles_h, nn = mt / (p.tiles_w * p.tiles_h);
+            const int x = xt * p.tw + ix, y = yt * p.th + iy, n = nn * p.tn + in_;
+            const bool valid = (x < p.Wout) && (y < p.Hout) && (n < p.N);
+            if (fast_stats && (n != cur_n || nt != cur_nt)) {
+                if (cur_n >= 0) {
+#pragma unroll
+                    for (int i = 0; i < BN / 32; ++i) {
+                        double *s = p.stats + ((long long)cur_n * p.Cout + cur_nt * BN + i * 32 + lane) * 2;
+                        atomicAdd(s, (double)racc1[i]);
+                        atomicAdd(s + 1, (double)racc2[i]);
+                        racc1[i] = 0.f; racc2[i] = 0.f;
+                    }
+                }
+                cur_n = nn * p.tn;   // tn == 1 -> the tile's image
+                cur_nt = nt;
+            }
+            const int buf = it & 1;
+            const uint32_t use = (uint32_t)(it >> 1);
+            mbar_wait(&tmem_full[buf], use & 1);
+            tcgen05_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BN);
+            int dy = 0, dx = 0;
+            if (p.tap_base_from_grid_y) { dy = blockIdx.y / p.mx; dx = blockIdx.y % p.mx; }
+            DT *orow = out + (((long long)n * p.Hfull + (long long)y * p.my + dy) * p.Wfull + (long long)x * p.mx + dx) * p.out_ps + nt * BN;
+#pragma unroll
+            for (int ch = 0; ch < BN / 32; ++ch) {
+                uint32_t r[32];
+                tmem_ld_32x32b_x32(taddr + ch * 32, r);
+                tmem_ld_wait();
+                if (ch == BN / 32 - 1) {
+                    // all of this thread's TMEM reads for the tile are done: release the accumulator buffer
+                    tcgen05_fence_before();
+                    mbar_arrive(&tmem_empty[buf]);
+                }
+                float v[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) + (p.bias ? __ldg(&p.bias[nt * BN + ch * 32 + j]) : 0.f);
+                uint32_t pk[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) pk[j] = pack2<DT>(v[2 * j], v[2 * j + 1]);
+                if (valid) {
+                    uint4 *dst = reinterpret_cast<uint4 *>(orow + ch * 32);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) dst[j] = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+                }
+                if (do_stats) {
+                    float a[32], b[32];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        const float2 f = unpack2<DT>(pk[j]);
+                        a[2 * j] = valid ? f.x : 0.f;
+                        a[2 * j + 1] = valid ? f.y : 0.f;
+                    }
+                    if (fast_stats) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) b[j] = a[j] * a[j];
+                        racc1[ch] += warp_transpose_sum32(a, lane);
+                        racc2[ch] += warp_transpose_sum32(b, lane);
+                    } else if (valid) {
+                        double *s = p.stats + ((long long)n * p.Cout + nt * BN + ch * 32) * 2;
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            atomicAdd(s + 2 * j, (double)a[j]);
+                            atomicAdd(s + 2 * j + 1, (double)a[j] * (double)a[j]);
+                        }
+                    }
+                }
+            }
+        }
+        if (fast_stats && cur_n >= 0) {
+#pragma unroll
+            for (int i = 0; i < BN / 32; ++i) {
+                double *s = p.stats + ((long long)cur_n * p.Cout + cur_nt * BN + i * 32 + lane) * 2;
+                atomicAdd(s, (double)racc1[i]);
+                atomicAdd(s + 1, (double)racc2[i]);
+            }
+        }
+    }
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kTmemCols) : "memory");
+    }
+}
+
+}  // namespace ts2d

@@ -1,0 +1,796 @@
+// The U-Net engine behind the C ABI: plan -> layer graph, weight repacking, workspace, TMA descriptors, forward.
+//
+// Mirrors what nnUNetPredictor.initialize_from_trained_model_folder builds (reference
+// ts2d/core/inference/nnu.py:149-166): dynamic_network_architectures PlainConvUNet =
+// encoder stages of [Conv2d k3 (first conv strided) -> InstanceNorm2d -> LeakyReLU], decoder levels of
+// ConvTranspose2d(k = stride) -> cat(up, skip) -> conv blocks, 1x1 seg head (deep supervision off).
+//
+// Data layout in HBM (activations NHWC, element = plan precision):
+//   cat[l]   [N][H_l][W_l][2*C_l]   channels [0,C_l) = up-sampled decoder input, [C_l,2C_l) = encoder skip; the
+//                                   encoder writes its stage output straight into the skip half and the transposed
+//                                   conv writes straight into the other half: torch.cat never happens.
+//   bott     [N][H_L][W_L][C_L]     bottleneck
+//   raw      conv output before normalisation (+ per-(n,c) sum / sum-of-squares in `stats`, double)
+//   tmpA/B   normalised intermediates / decoder stage outputs
+#include <algorithm>
+#include <map>
+#include <vector>
+
+#include "conv_tc.cuh"
+#include "unet_kernels.cuh"
+
+namespace ts2d {
+
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                    const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static PFN_encodeTiled get_encode_fn() {
+    static PFN_encodeTiled fn = nullptr;
+    if (!fn) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = (PFN_encodeTiled)p;
+    }
+    return fn;
+}
+
+struct Param {
+    std::vector<float> host;
+    bool have = false;
+    float *dev = nullptr;
+};
+
+struct ConvLayer {
+    std::string name;           // "enc{s}.{i}" / "dec{d}.{i}"
+    int cin = 0, cout = 0, kh = 3, kw = 3, sh = 1, sw = 1;
+    int Hin = 0, Win = 0, Hout = 0, Wout = 0;
+    Param w, b, gamma, beta;    // upstream layouts: w OIHW
+    float *w_direct = nullptr;  // [tap][Cin][Cout] fp32
+    void *w_tc = nullptr;       // [tap][Cout][Cin] bf16/fp16
+    const void *in = nullptr;   // set per forward for the first layer
+    long long in_ps = 0;
+    void *norm_out = nullptr;
+    long long out_ps = 0;
+    double *stats = nullptr;
+    bool tc = false;
+    int bn = 0, kc = 0, enc_n = 0;
+    CUtensorMap tmA, tmB;
+    bool first = false;         // reads the caller's tiles: tmA encoded per forward
+};
+
+struct UpLayer {
+    std::string name;           // "up{d}"
+    int cin = 0, cout = 0, sh = 2, sw = 2, Hin = 0, Win = 0;
+    Param w, b;                 // upstream: [Cin][Cout][kh][kw]
+    float *w_direct = nullptr;  // [tap][Cin][Cout]
+    void *w_tc = nullptr;       // [tap][Cout][Cin]
+    const void *in = nullptr;
+    void *out = nullptr;
+    long long out_ps = 0;
+    bool tc = false;
+    int bn = 0, kc = 0, enc_n = 0;
+    CUtensorMap tmA, tmB;
+};
+
+struct Op { int kind; int idx; };   // 0 = conv (+norm), 1 = up
+
+}  // namespace ts2d
+
+using namespace ts2d;
+
+struct ts2d_unet {
+    ts2d_unet_plan plan;
+    int L = 0;
+    std::vector<int> H, W, C;
+    std::vector<ConvLayer> convs;
+    std::vector<UpLayer> ups;
+    std::vector<Op> ops;
+    Param head_w, head_b;
+    bool finalized = false;
+    size_t es = 2;
+    // workspace
+    uint8_t *arena = nullptr;
+    size_t arena_bytes = 0;
+    std::vector<void *> cat;
+    void *bott = nullptr, *raw = nullptr, *tmpA = nullptr, *tmpB = nullptr;
+    double *stats_arena = nullptr;
+    size_t stats_bytes = 0;
+    void *features = nullptr;     // last decoder output [N][P][P][C0]
+    int last_batch = 0;
+    long long launches = 0;
+    bool profiling = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
+    int prof_used = 0;
+};
+
+namespace ts2d {
+
+static void choose_tile(int Hout, int Wout, int N, int &tw, int &th, int &tn) {
+    double best = 1e30;
+    tw = 128; th = 1; tn = 1;
+    for (int cw = 128; cw >= 1; cw >>= 1) {
+        if (cw > 1 && cw / 2 >= Wout) continue;          // do not take a width with > 50% overhang when a smaller one fits
+        int ch = 128 / cw;
+        int hh = 1;
+        while (hh < ch && hh < Hout) hh <<= 1;
+        ch = std::min(ch, hh);
+        const int cn = 128 / (cw * ch);
+        const double covered = (double)ceil_div(Wout, cw) * cw * ceil_div(Hout, ch) * ch * ceil_div(N, cn) * cn;
+        const double waste = covered / ((double)Wout * Hout * N);
+        if (waste < best - 1e-9) { best = waste; tw = cw; th = ch; tn = cn; }
+    }
+}
+
+static int choose_bn(int cout, long long m_tiles) {
+    int best_bn = 32;
+    double best_eff = -1;
+    for (int bn : {256, 128, 64, 32}) {
+        if (cout % bn) continue;
+        const long long tiles = m_tiles * (cout / bn);
+        const double eff = (double)tiles / ((double)ceil_div(tiles, kNumSMs) * kNumSMs);
+        // larger BN halves the A re-reads; require a clear occupancy win to go smaller
+        if (eff > best_eff * 1.15) { best_eff = eff; best_bn = bn; }
+    }
+    return best_bn;
+}
+
+static int encode_map(CUtensorMap *tm, void *base, int rank, const cuuint64_t *dims, const cuuint64_t *strides_bytes, const cuuint32_t *box,
+                      int kc, size_t es, bool is_bf16) {
+    PFN_encodeTiled fn = get_encode_fn();
+    if (!fn) { set_error("cuTensorMapEncodeTiled entry point not available"); return TS2D_ERR_DEVICE; }
+    cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+    (void)es;
+    const CUtensorMapSwizzle sw = kc == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+    CUresult r = fn(tm, is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, (cuuint32_t)rank, base, dims,
+                    strides_bytes, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed with CUresult %d (rank %d)", (int)r, rank); return TS2D_ERR_CUDA; }
+    return TS2D_OK;
+}
+
+// activation map for a conv input: stride 1 -> (C, W, H, N); stride 2 -> parity view (px*ps + C, W/2, 2, H/2, N)
+static int encode_act_map(CUtensorMap *tm, const void *base, long long ps, int Cin, int Hin, int Win, int Nmax, bool stride2, int kc, int tw, int th,
+                          int tn, size_t es, bool is_bf16) {
+    if (!stride2) {
+        cuuint64_t dims[4] = {(cuuint64_t)Cin, (cuuint64_t)Win, (cuuint64_t)Hin, (cuuint64_t)Nmax};
+        cuuint64_t str[3] = {(cuuint64_t)(ps * es), (cuuint64_t)(ps * es * Win), (cuuint64_t)(ps * es * Win * Hin)};
+        cuuint32_t box[4] = {(cuuint32_t)kc, (cuuint32_t)tw, (cuuint32_t)th, (cuuint32_t)tn};
+        return encode_map(tm, const_cast<void *>(base), 4, dims, str, box, kc, es, is_bf16);
+    }
+    cuuint64_t dims[5] = {(cuuint64_t)(ps + Cin), (cuuint64_t)(Win / 2), 2, (cuuint64_t)(Hin / 2), (cuuint64_t)Nmax};
+    cuuint64_t str[4] = {(cuuint64_t)(2 * ps * es), (cuuint64_t)(ps * es * Win), (cuuint64_t)(2 * ps * es * Win), (cuuint64_t)(ps * es * Win * Hin)};
+    cuuint32_t box[5] = {(cuuint32_t)kc, (cuuint32_t)tw, 1, (cuuint32_t)th, (cuuint32_t)tn};
+    return encode_map(tm, const_cast<void *>(base), 5, dims, str, box, kc, es, is_bf16);
+}
+
+static int encode_w_map(CUtensorMap *tm, const void *base, int Cin, int Cout, int taps, int kc, int bn, size_t es, bool is_bf16) {
+    cuuint64_t dims[3] = {(cuuint64_t)Cin, (cuuint64_t)Cout, (cuuint64_t)taps};
+    cuuint64_t str[2] = {(cuuint64_t)(Cin * es), (cuuint64_t)(Cin * es * Cout)};
+    cuuint32_t box[3] = {(cuuint32_t)kc, (cuuint32_t)bn, 1};
+    return encode_map(tm, const_cast<void *>(base), 3, dims, str, box, kc, es, is_bf16);
+}
+
+template <int BN, int KC, typename DT>
+static int launch_tc_inst(const CUtensorMap &tmA, const CUtensorMap &tmB, const ConvTcParams &p, int grid_y, cudaStream_t st) {
+    static bool attr_set = false;
+    constexpr int smem = tc_smem_bytes<BN, KC>();
+    if (!attr_set) {
+        TS2D_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<BN, KC, DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_set = true;
+    }
+    const int m_tiles = p.tiles_n * p.tiles_h * p.tiles_w;
+    const int total = m_tiles * p.n_tiles_n;
+    const int gx = std::max(1, std::min(total, kNumSMs / grid_y));
+    conv_tc_kernel<BN, KC, DT><<<dim3(gx, grid_y), 192, smem, st>>>(tmA, tmB, p);
+    TS2D_LAUNCH_CHECK();
+    return TS2D_OK;
+}
+template <typename DT>
+static int launch_tc(int bn, int kc, const CUtensorMap &tmA, const CUtensorMap &tmB, const ConvTcParams &p, int grid_y, cudaStream_t st) {
+#define TS2D_TC_CASE(B, K) if (bn == B && kc == K) return launch_tc_inst<B, K, DT>(tmA, tmB, p, grid_y, st);
+    TS2D_TC_CASE(32, 32) TS2D_TC_CASE(64, 32) TS2D_TC_CASE(128, 32) TS2D_TC_CASE(256, 32)
+    TS2D_TC_CASE(32, 64) TS2D_TC_CASE(64, 64) TS2D_TC_CASE(128, 64) TS2D_TC_CASE(256, 64)
+#undef TS2D_TC_CASE
+    set_error("no tensor-core conv instantiation for BN=%d KC=%d", bn, kc);
+    return TS2D_ERR_UNSUPPORTED;
+}
+
+template <typename T> static int launch_direct(const DirectConvParams &p, int N, cudaStream_t st) {
+    const int npix = p.Hout * p.Wout;
+    int iters = npix >= 32 * 64 ? 8 : 1;
+    DirectConvParams q = p;
+    q.pix_iters = iters;
+    dim3 grid(ceil_div(npix, 32 * iters), ceil_div(p.Cout, 32), N);
+    conv_direct_kernel<T><<<grid, 128, 0, st>>>(q);
+    TS2D_LAUNCH_CHECK();
+    return TS2D_OK;
+}
+static int launch_direct_any(int precision, const DirectConvParams &p, int N, cudaStream_t st) {
+    if (precision == TS2D_PREC_F32) return launch_direct<float>(p, N, st);
+    if (precision == TS2D_PREC_BF16) return launch_direct<__nv_bfloat16>(p, N, st);
+    return launch_direct<__half>(p, N, st);
+}
+
+template <typename T>
+static int launch_norm(const void *raw, const double *stats, const float *g, const float *b, void *out, long long out_ps, int HW, int C, float eps,
+                       float slope, int N, cudaStream_t st) {
+    int ppb = std::max(32, ceil_div(HW, std::max(1, (kNumSMs * 4) / std::max(1, N))));
+    ppb = std::min(ppb, 4096);
+    dim3 grid(ceil_div(HW, ppb), N);
+    norm_act_kernel<T><<<grid, 256, 2 * C * sizeof(float), st>>>((const T *)raw, stats, g, b, (T *)out, out_ps, HW, C, eps, slope, ppb);
+    TS2D_LAUNCH_CHECK();
+    return TS2D_OK;
+}
+static int launch_norm_any(int precision, const void *raw, const double *stats, const float *g, const float *b, void *out, long long out_ps, int HW,
+                           int C, float eps, float slope, int N, cudaStream_t st) {
+    if (precision == TS2D_PREC_F32) return launch_norm<float>(raw, stats, g, b, out, out_ps, HW, C, eps, slope, N, st);
+    if (precision == TS2D_PREC_BF16) return launch_norm<__nv_bfloat16>(raw, stats, g, b, out, out_ps, HW, C, eps, slope, N, st);
+    return launch_norm<__half>(raw, stats, g, b, out, out_ps, HW, C, eps, slope, N, st);
+}
+
+static int upload(Param &p) {
+    if (!p.have) return TS2D_OK;
+    if (!p.dev) TS2D_CHECK_CUDA(cudaMalloc(&p.dev, p.host.size() * sizeof(float)));
+    TS2D_CHECK_CUDA(cudaMemcpy(p.dev, p.host.data(), p.host.size() * sizeof(float), cudaMemcpyHostToDevice));
+    return TS2D_OK;
+}
+
+// upstream conv weight OIHW -> direct [tap][Cin][Cout] fp32 and tc [tap][Cout][Cin] DT
+static int repack_conv(const std::vector<float> &w, int cout, int cin, int taps, bool transposed_src, int precision, bool want_tc, float **w_direct,
+                       void **w_tc) {
+    std::vector<float> d((size_t)taps * cin * cout);
+    for (int o = 0; o < cout; ++o)
+        for (int i = 0; i < cin; ++i)
+            for (int t = 0; t < taps; ++t) {
+                // conv: [o][i][t]; transposed conv: [i][o][t]
+                const float v = transposed_src ? w[((size_t)i * cout + o) * taps + t] : w[((size_t)o * cin + i) * taps + t];
+                d[((size_t)t * cin + i) * cout + o] = v;
+            }
+    if (!*w_direct) TS2D_CHECK_CUDA(cudaMalloc(w_direct, d.size() * sizeof(float)));
+    TS2D_CHECK_CUDA(cudaMemcpy(*w_direct, d.data(), d.size() * sizeof(float), cudaMemcpyHostToDevice));
+    if (want_tc) {
+        std::vector<uint16_t> h((size_t)taps * cin * cout);
+        for (int o = 0; o < cout; ++o)
+            for (int i = 0; i < cin; ++i)
+                for (int t = 0; t < taps; ++t) {
+                    const float v = d[((size_t)t * cin + i) * cout + o];
+                    uint16_t bits;
+                    if (precision == TS2D_PREC_BF16) { __nv_bfloat16 x = __float2bfloat16_rn(v); memcpy(&bits, &x, 2); }
+                    else { __half x = __float2half_rn(v); memcpy(&bits, &x, 2); }
+                    h[((size_t)t * cout + o) * cin + i] = bits;
+                }
+        if (!*w_tc) TS2D_CHECK_CUDA(cudaMalloc(w_tc, h.size() * 2));
+        TS2D_CHECK_CUDA(cudaMemcpy(*w_tc, h.data(), h.size() * 2, cudaMemcpyHostToDevice));
+    }
+    return TS2D_OK;
+}
+
+static bool tc_eligible(const ts2d_unet_plan &pl, int cin, int cout, int kh, int kw, int sh, int sw, int Hin, int Win, long long in_ps) {
+    if (!pl.use_tensor_cores || pl.precision == TS2D_PREC_F32) return false;
+    if (cin % 32 || cout % 32 || in_ps % 8) return false;
+    if (!((kh == 3 && kw == 3) || (kh == 1 && kw == 1))) return false;
+    if (sh == 1 && sw == 1) return true;
+    if (sh == 2 && sw == 2 && Hin % 2 == 0 && Win % 2 == 0) return true;
+    return false;
+}
+
+static void fill_tc_params(ConvTcParams &p, int N, int Hout, int Wout, int cout, int cin, int kc, int bn, int taps, int kw, int pad_h, int pad_w,
+                           bool stride2, long long in_ps) {
+    memset(&p, 0, sizeof(p));
+    p.N = N; p.Hout = Hout; p.Wout = Wout; p.Cout = cout;
+    p.cin_chunks = cin / kc;
+    p.taps = taps; p.kw = kw; p.pad_h = pad_h; p.pad_w = pad_w;
+    p.stride2 = stride2 ? 1 : 0;
+    p.in_ps = (int)in_ps;
+    p.n_tiles_n = cout / bn;
+    p.my = 1; p.mx = 1; p.Hfull = Hout; p.Wfull = Wout;
+}
+
+}  // namespace ts2d
+
+// =========================================================================================================
+extern "C" int ts2d_unet_create(const ts2d_unet_plan *pl, ts2d_unet **out) {
+    TS2D_REQUIRE(pl && out, "ts2d_unet_create: null pointer");
+    TS2D_REQUIRE(pl->n_stages >= 2 && pl->n_stages <= TS2D_MAX_STAGES, "ts2d_unet_create: n_stages must be 2..%d", TS2D_MAX_STAGES);
+    TS2D_REQUIRE(pl->in_channels >= 1 && pl->num_heads >= 1 && pl->max_batch >= 1, "ts2d_unet_create: bad channels/heads/batch");
+    TS2D_REQUIRE(pl->precision >= 0 && pl->precision <= 2, "ts2d_unet_create: bad precision");
+    TS2D_REQUIRE(pl->patch_h > 0 && pl->patch_w > 0, "ts2d_unet_create: bad patch size");
+    const int L = pl->n_stages;
+    ts2d_unet *u = new ts2d_unet();
+    u->plan = *pl;
+    u->L = L;
+    u->es = prec_size(pl->precision);
+    u->H.resize(L); u->W.resize(L); u->C.resize(L);
+    int h = pl->patch_h, w = pl->patch_w;
+    for (int s = 0; s < L; ++s) {
+        const int kh = pl->kernel_sizes[s][0], kw = pl->kernel_sizes[s][1], sh = pl->strides[s][0], sw = pl->strides[s][1];
+        if (!(kh % 2 == 1 && kw % 2 == 1 && sh >= 1 && sw >= 1 && pl->features[s] >= 1 && pl->n_conv_enc[s] >= 1)) {
+            delete u; set_error("ts2d_unet_create: bad stage %d description", s); return TS2D_ERR_ARG;
+        }
+        if (h % sh || w % sw) { delete u; set_error("ts2d_unet_create: patch size is not divisible by the strides at stage %d", s); return TS2D_ERR_ARG; }
+        h /= sh; w /= sw;
+        u->H[s] = h; u->W[s] = w; u->C[s] = pl->features[s];
+    }
+    // encoder
+    int cin = pl->in_channels, hin = pl->patch_h, win = pl->patch_w;
+    for (int s = 0; s < L; ++s) {
+        for (int i = 0; i < pl->n_conv_enc[s]; ++i) {
+            ConvLayer c;
+            c.name = "enc" + std::to_string(s) + "." + std::to_string(i);
+            c.cin = cin; c.cout = u->C[s];
+            c.kh = pl->kernel_sizes[s][0]; c.kw = pl->kernel_sizes[s][1];
+            c.sh = i == 0 ? pl->strides[s][0] : 1; c.sw = i == 0 ? pl->strides[s][1] : 1;
+            c.Hin = hin; c.Win = win; c.Hout = u->H[s]; c.Wout = u->W[s];
+            c.first = (s == 0 && i == 0);
+            u->ops.push_back({0, (int)u->convs.size()});
+            u->convs.push_back(c);
+            cin = u->C[s]; hin = u->H[s]; win = u->W[s];
+        }
+    }
+    // decoder
+    for (int d = 0; d < L - 1; ++d) {
+        const int l = L - 2 - d;
+        if (pl->n_conv_dec[d] < 1) { delete u; set_error("ts2d_unet_create: n_conv_dec[%d] < 1", d); return TS2D_ERR_ARG; }
+        UpLayer up;
+        up.name = "up" + std::to_string(d);
+        up.cin = u->C[l + 1]; up.cout = u->C[l];
+        up.sh = pl->strides[l + 1][0]; up.sw = pl->strides[l + 1][1];
+        up.Hin = u->H[l + 1]; up.Win = u->W[l + 1];
+        u->ops.push_back({1, (int)u->ups.size()});
+        u->ups.push_back(up);
+        int ci = 2 * u->C[l];
+        for (int i = 0; i < pl->n_conv_dec[d]; ++i) {
+            ConvLayer c;
+            c.name = "dec" + std::to_string(d) + "." + std::to_string(i);
+            c.cin = ci; c.cout = u->C[l];
+            c.kh = pl->kernel_sizes[l][0]; c.kw = pl->kernel_sizes[l][1];
+            c.Hin = c.Hout = u->H[l]; c.Win = c.Wout = u->W[l];
+            u->ops.push_back({0, (int)u->convs.size()});
+            u->convs.push_back(c);
+            ci = u->C[l];
+        }
+    }
+    *out = u;
+    return TS2D_OK;
+}
+
+static ConvLayer *find_conv(ts2d_unet *u, const std::string &name) {
+    for (auto &c : u->convs) if (c.name == name) return &c;
+    return nullptr;
+}
+
+static int set_param(Param &p, const float *data, int64_t count, int64_t expect, const char *name) {
+    if (count != expect) { set_error("ts2d_unet_set_weight: %s has %lld elements, expected %lld", name, (long long)count, (long long)expect); return TS2D_ERR_ARG; }
+    p.host.assign(data, data + count);
+    p.have = true;
+    return TS2D_OK;
+}
+
+extern "C" int ts2d_unet_set_weight(ts2d_unet *u, const char *name, const float *data, int64_t count) {
+    TS2D_REQUIRE(u && name && data, "ts2d_unet_set_weight: null pointer");
+    std::string nm(name);
+    if (nm.find("all_modules") != std::string::npos || nm.rfind("decoder.encoder.", 0) == 0) return 1;
+    int s = 0, i = 0, d = 0;
+    char tail[64];
+    const bool is_enc = sscanf(name, "encoder.stages.%d.0.convs.%d.%63s", &s, &i, tail) == 3;
+    const bool is_dec = !is_enc && sscanf(name, "decoder.stages.%d.convs.%d.%63s", &s, &i, tail) == 3;
+    if (is_enc || is_dec) {
+        ConvLayer *c = find_conv(u, std::string(is_enc ? "enc" : "dec") + std::to_string(s) + "." + std::to_string(i));
+        if (!c) { set_error("ts2d_unet_set_weight: no layer for %s", name); return TS2D_ERR_ARG; }
+        const std::string t(tail);
+        if (t == "conv.weight") return set_param(c->w, data, count, (int64_t)c->cout * c->cin * c->kh * c->kw, name);
+        if (t == "conv.bias") return set_param(c->b, data, count, c->cout, name);
+        if (t == "norm.weight") return set_param(c->gamma, data, count, c->cout, name);
+        if (t == "norm.bias") return set_param(c->beta, data, count, c->cout, name);
+        return 1;
+    }
+    if (sscanf(name, "decoder.transpconvs.%d.%63s", &d, tail) == 2) {
+        if (d < 0 || d >= (int)u->ups.size()) { set_error("ts2d_unet_set_weight: no transposed conv %d", d); return TS2D_ERR_ARG; }
+        UpLayer &up = u->ups[d];
+        const std::string t(tail);
+        if (t == "weight") return set_param(up.w, data, count, (int64_t)up.cin * up.cout * up.sh * up.sw, name);
+        if (t == "bias") return set_param(up.b, data, count, up.cout, name);
+        return 1;
+    }
+    if (sscanf(name, "decoder.seg_layers.%d.%63s", &d, tail) == 2) {
+        if (d != u->L - 2) return 1;   // deep-supervision heads are unused at inference
+        const std::string t(tail);
+        if (t == "weight") return set_param(u->head_w, data, count, (int64_t)u->plan.num_heads * u->C[0], name);
+        if (t == "bias") return set_param(u->head_b, data, count, u->plan.num_heads, name);
+        return 1;
+    }
+    return 1;
+}
+
+extern "C" int ts2d_unet_finalize(ts2d_unet *u) {
+    TS2D_REQUIRE(u, "ts2d_unet_finalize: null handle");
+    const ts2d_unet_plan &pl = u->plan;
+    const int L = u->L, N = pl.max_batch;
+    const size_t es = u->es;
+    for (auto &c : u->convs)
+        if (!c.w.have) { set_error("ts2d_unet_finalize: missing weight for %s", c.name.c_str()); return TS2D_ERR_STATE; }
+    for (auto &up : u->ups)
+        if (!up.w.have) { set_error("ts2d_unet_finalize: missing weight for %s", up.name.c_str()); return TS2D_ERR_STATE; }
+    if (!u->head_w.have) { set_error("ts2d_unet_finalize: missing seg head weight (decoder.seg_layers.%d.weight)", L - 2); return TS2D_ERR_STATE; }
+    int dev = 0;
+    cudaDeviceProp prop;
+    TS2D_CHECK_CUDA(cudaGetDevice(&dev));
+    TS2D_CHECK_CUDA(cudaGetDeviceProperties(&prop, dev));
+    if (prop.major != 10) { set_error("ts2d_unet_finalize: device %d is sm_%d%d, this library contains sm_100a code only", dev, prop.major, prop.minor); return TS2D_ERR_DEVICE; }
+
+    // ---- workspace ----
+    auto align = [](size_t v) { return (v + 1023) & ~(size_t)1023; };
+    size_t off = 0;
+    std::vector<size_t> cat_off(L - 1);
+    for (int l = 0; l < L - 1; ++l) { cat_off[l] = off; off += align((size_t)N * u->H[l] * u->W[l] * 2 * u->C[l] * es); }
+    const size_t bott_off = off; off += align((size_t)N * u->H[L - 1] * u->W[L - 1] * u->C[L - 1] * es);
+    size_t max_act = 0;
+    for (auto &c : u->convs) max_act = std::max(max_act, (size_t)N * c.Hout * c.Wout * c.cout * es);
+    const size_t raw_off = off; off += align(max_act);
+    const size_t a_off = off; off += align(max_act);
+    const size_t b_off = off; off += align(max_act);
+    const size_t stats_off = off;
+    size_t sbytes = 0;
+    for (auto &c : u->convs) sbytes += align((size_t)N * c.cout * 2 * sizeof(double));
+    off += sbytes;
+    if (u->arena) cudaFree(u->arena);
+    TS2D_CHECK_CUDA(cudaMalloc(&u->arena, off));
+    TS2D_CHECK_CUDA(cudaMemset(u->arena, 0, off));
+    u->arena_bytes = off;
+    u->cat.resize(L - 1);
+    for (int l = 0; l < L - 1; ++l) u->cat[l] = u->arena + cat_off[l];
+    u->bott = u->arena + bott_off; u->raw = u->arena + raw_off; u->tmpA = u->arena + a_off; u->tmpB = u->arena + b_off;
+    u->stats_arena = reinterpret_cast<double *>(u->arena + stats_off);
+    u->stats_bytes = sbytes;
+    size_t so = 0;
+    for (auto &c : u->convs) { c.stats = reinterpret_cast<double *>(u->arena + stats_off + so); so += align((size_t)N * c.cout * 2 * sizeof(double)); }
+
+    // ---- wiring ----
+    size_t ci = 0;
+    const void *cur = nullptr; long long cur_ps = pl.in_channels;
+    for (int s = 0; s < L; ++s) {
+        for (int i = 0; i < pl.n_conv_enc[s]; ++i, ++ci) {
+            ConvLayer &c = u->convs[ci];
+            c.in = cur; c.in_ps = cur_ps;
+            const bool last = i == pl.n_conv_enc[s] - 1;
+            if (last) {
+                if (s < L - 1) { c.norm_out = (uint8_t *)u->cat[s] + (size_t)u->C[s] * es; c.out_ps = 2 * u->C[s]; }
+                else { c.norm_out = u->bott; c.out_ps = u->C[s]; }
+            } else { c.norm_out = u->tmpA; c.out_ps = u->C[s]; }
+            cur = c.norm_out; cur_ps = c.out_ps;
+        }
+    }
+    const void *lres = u->bott;
+    for (int d = 0; d < L - 1; ++d) {
+        const int l = L - 2 - d;
+        UpLayer &up = u->ups[d];
+        up.in = lres; up.out = u->cat[l]; up.out_ps = 2 * u->C[l];
+        cur = u->cat[l]; cur_ps = 2 * u->C[l];
+        for (int i = 0; i < pl.n_conv_dec[d]; ++i, ++ci) {
+            ConvLayer &c = u->convs[ci];
+            c.in = cur; c.in_ps = cur_ps;
+            const bool last = i == pl.n_conv_dec[d] - 1;
+            c.norm_out = last ? u->tmpB : u->tmpA; c.out_ps = u->C[l];
+            cur = c.norm_out; cur_ps = c.out_ps;
+        }
+        lres = u->tmpB;
+    }
+    u->features = u->tmpB;
+
+    // ---- parameters ----
+    int rc;
+    for (auto &c : u->convs) {
+        c.tc = tc_eligible(pl, c.cin, c.cout, c.kh, c.kw, c.sh, c.sw, c.Hin, c.Win, c.in_ps);
+        if ((rc = repack_conv(c.w.host, c.cout, c.cin, c.kh * c.kw, false, pl.precision, c.tc, &c.w_direct, &c.w_tc))) return rc;
+        if ((rc = upload(c.b)) || (rc = upload(c.gamma)) || (rc = upload(c.beta))) return rc;
+        if (c.tc) c.kc = (c.cin % 64 == 0) ? 64 : 32;
+        c.enc_n = 0;
+    }
+    for (auto &up : u->ups) {
+        up.tc = tc_eligible(pl, up.cin, up.cout, 1, 1, 1, 1, up.Hin, up.Win, up.cin);
+        if ((rc = repack_conv(up.w.host, up.cout, up.cin, up.sh * up.sw, true, pl.precision, up.tc, &up.w_direct, &up.w_tc))) return rc;
+        if ((rc = upload(up.b))) return rc;
+        if (up.tc) up.kc = (up.cin % 64 == 0) ? 64 : 32;
+        up.enc_n = 0;
+    }
+    if ((rc = upload(u->head_w)) || (rc = upload(u->head_b))) return rc;
+    u->finalized = true;
+    u->last_batch = 0;
+    return TS2D_OK;
+}
+
+extern "C" size_t ts2d_unet_workspace_bytes(const ts2d_unet *u) { return u ? u->arena_bytes : 0; }
+extern "C" int64_t ts2d_unet_launch_count(const ts2d_unet *u) { return u ? u->launches : 0; }
+
+extern "C" double ts2d_unet_flops(const ts2d_unet *u, int batch) {
+    if (!u) return 0.0;
+    double fl = 0.0;
+    for (auto &c : u->convs) fl += 2.0 * c.Hout * c.Wout * c.kh * c.kw * (double)c.cin * c.cout;
+    for (auto &up : u->ups) fl += 2.0 * (double)up.Hin * up.sh * up.Win * up.sw * up.cin * up.cout;
+    fl += 2.0 * (double)u->plan.patch_h * u->plan.patch_w * u->C[0] * u->plan.num_heads;
+    return fl * batch;
+}
+
+namespace ts2d {
+
+static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
+    const ts2d_unet_plan &pl = u->plan;
+    const size_t es = u->es;
+    const bool is_bf16 = pl.precision == TS2D_PREC_BF16;
+    int rc;
+    if (u->profiling) {
+        if (u->prof_used >= (int)u->prof_events.size()) {
+            cudaEvent_t a, b;
+            TS2D_CHECK_CUDA(cudaEventCreate(&a));
+            TS2D_CHECK_CUDA(cudaEventCreate(&b));
+            u->prof_events.push_back({a, b});
+        }
+        TS2D_CHECK_CUDA(cudaEventRecord(u->prof_events[u->prof_used].first, st));
+    }
+    if (c.tc) {
+        ConvTcParams p;
+        const bool s2 = c.sh == 2;
+        int tw, th, tn;
+        choose_tile(c.Hout, c.Wout, N, tw, th, tn);
+        const long long m_tiles = (long long)ceil_div(c.Wout, tw) * ceil_div(c.Hout, th) * ceil_div(N, tn);
+        const int bn = choose_bn(c.cout, m_tiles);
+        fill_tc_params(p, N, c.Hout, c.Wout, c.cout, c.cin, c.kc, bn, c.kh * c.kw, c.kw, (c.kh - 1) / 2, (c.kw - 1) / 2, s2, c.in_ps);
+        p.tw = tw; p.th = th; p.tn = tn;
+        p.tiles_w = ceil_div(c.Wout, tw); p.tiles_h = ceil_div(c.Hout, th); p.tiles_n = ceil_div(N, tn);
+        p.out_ps = c.cout; p.out = u->raw; p.bias = c.b.dev; p.stats = c.stats;
+        // descriptors depend on (input pointer, batch-dependent tile box, BN): cache by (N, bn)
+        if (c.first || c.bn != bn || c.enc_n != N) {
+            if ((rc = encode_act_map(&c.tmA, c.in, c.in_ps, c.cin, c.Hin, c.Win, pl.max_batch, s2, c.kc, tw, th, tn, es, is_bf16))) return rc;
+            if ((rc = encode_w_map(&c.tmB, c.w_tc, c.cin, c.cout, c.kh * c.kw, c.kc, bn, es, is_bf16))) return rc;
+            c.bn = bn;
+            c.enc_n = N;
+        }
+        rc = is_bf16 ? launch_tc<__nv_bfloat16>(bn, c.kc, c.tmA, c.tmB, p, 1, st) : launch_tc<__half>(bn, c.kc, c.tmA, c.tmB, p, 1, st);
+        if (rc) return rc;
+    } else {
+        DirectConvParams p;
+        memset(&p, 0, sizeof(p));
+        p.in = c.in; p.in_ps = c.in_ps; p.Hin = c.Hin; p.Win = c.Win; p.Cin = c.cin;
+        p.w = c.w_direct; p.bias = c.b.dev;
+        p.out = u->raw; p.out_ps = c.cout; p.Hout = c.Hout; p.Wout = c.Wout; p.Cout = c.cout;
+        p.kh = c.kh; p.kw = c.kw; p.sh = c.sh; p.sw = c.sw; p.ph = (c.kh - 1) / 2; p.pw = (c.kw - 1) / 2;
+        p.my = 1; p.mx = 1; p.dy = 0; p.dx = 0; p.Hfull = c.Hout; p.Wfull = c.Wout;
+        p.stats = c.stats;
+        if ((rc = launch_direct_any(pl.precision, p, N, st))) return rc;
+    }
+    u->launches++;
+    if (u->profiling) {
+        TS2D_CHECK_CUDA(cudaEventRecord(u->prof_events[u->prof_used].second, st));
+        u->prof_used++;
+    }
+    rc = launch_norm_any(pl.precision, u->raw, c.stats, c.gamma.dev, c.beta.dev, c.norm_out, c.out_ps, c.Hout * c.Wout, c.cout, pl.eps,
+                         pl.negative_slope, N, st);
+    if (rc) return rc;
+    u->launches++;
+    return TS2D_OK;
+}
+
+static int run_up(ts2d_unet *u, UpLayer &up, int N, cudaStream_t st) {
+    const ts2d_unet_plan &pl = u->plan;
+    const size_t es = u->es;
+    const bool is_bf16 = pl.precision == TS2D_PREC_BF16;
+    int rc;
+    if (u->profiling) {
+        if (u->prof_used >= (int)u->prof_events.size()) {
+            cudaEvent_t a, b;
+            TS2D_CHECK_CUDA(cudaEventCreate(&a));
+            TS2D_CHECK_CUDA(cudaEventCreate(&b));
+            u->prof_events.push_back({a, b});
+        }
+        TS2D_CHECK_CUDA(cudaEventRecord(u->prof_events[u->prof_used].first, st));
+    }
+    if (up.tc) {
+        ConvTcParams p;
+        int tw, th, tn;
+        choose_tile(up.Hin, up.Win, N, tw, th, tn);
+        const long long m_tiles = (long long)ceil_div(up.Win, tw) * ceil_div(up.Hin, th) * ceil_div(N, tn);
+        const int taps = up.sh * up.sw;
+        const int bn = choose_bn(up.cout, m_tiles * taps);
+        fill_tc_params(p, N, up.Hin, up.Win, up.cout, up.cin, up.kc, bn, 1, 1, 0, 0, false, up.cin);
+        p.tw = tw; p.th = th; p.tn = tn;
+        p.tiles_w = ceil_div(up.Win, tw); p.tiles_h = ceil_div(up.Hin, th); p.tiles_n = ceil_div(N, tn);
+        p.my = up.sh; p.mx = up.sw; p.Hfull = up.Hin * up.sh; p.Wfull = up.Win * up.sw;
+        p.out_ps = up.out_ps; p.out = up.out; p.bias = up.b.dev; p.stats = nullptr;
+        p.tap_base_from_grid_y = 1;
+        if (up.bn != bn || up.enc_n != N) {
+            if ((rc = encode_act_map(&up.tmA, up.in, up.cin, up.cin, up.Hin, up.Win, pl.max_batch, false, up.kc, tw, th, tn, es, is_bf16))) return rc;
+            if ((rc = encode_w_map(&up.tmB, up.w_tc, up.cin, up.cout, taps, up.kc, bn, es, is_bf16))) return rc;
+            up.bn = bn;
+            up.enc_n = N;
+        }
+        rc = is_bf16 ? launch_tc<__nv_bfloat16>(bn, up.kc, up.tmA, up.tmB, p, taps, st) : launch_tc<__half>(bn, up.kc, up.tmA, up.tmB, p, taps, st);
+        if (rc) return rc;
+        u->launches++;
+    } else {
+        for (int dy = 0; dy < up.sh; ++dy)
+            for (int dx = 0; dx < up.sw; ++dx) {
+                DirectConvParams p;
+                memset(&p, 0, sizeof(p));
+                p.in = up.in; p.in_ps = up.cin; p.Hin = up.Hin; p.Win = up.Win; p.Cin = up.cin;
+                p.w = up.w_direct + (size_t)(dy * up.sw + dx) * up.cin * up.cout; p.bias = up.b.dev;
+                p.out = up.out; p.out_ps = up.out_ps; p.Hout = up.Hin; p.Wout = up.Win; p.Cout = up.cout;
+                p.kh = 1; p.kw = 1; p.sh = 1; p.sw = 1; p.ph = 0; p.pw = 0;
+                p.my = up.sh; p.mx = up.sw; p.dy = dy; p.dx = dx; p.Hfull = up.Hin * up.sh; p.Wfull = up.Win * up.sw;
+                p.stats = nullptr;
+                if ((rc = launch_direct_any(pl.precision, p, N, st))) return rc;
+                u->launches++;
+            }
+    }
+    if (u->profiling) {
+        TS2D_CHECK_CUDA(cudaEventRecord(u->prof_events[u->prof_used].second, st));
+        u->prof_used++;
+    }
+    return TS2D_OK;
+}
+
+static int forward_impl(ts2d_unet *u, const void *x, int batch, const char *stop_layer, float *debug_out, cudaStream_t st) {
+    if (!u->finalized) { set_error("ts2d_unet_forward: engine not finalised"); return TS2D_ERR_STATE; }
+    if (batch < 1 || batch > u->plan.max_batch) { set_error("ts2d_unet_forward: batch %d outside 1..%d", batch, u->plan.max_batch); return TS2D_ERR_STATE; }
+    if (((uintptr_t)x) % 16) { set_error("ts2d_unet_forward: input tiles must be 16-byte aligned"); return TS2D_ERR_ARG; }
+    TS2D_CHECK_CUDA(cudaMemsetAsync(u->stats_arena, 0, u->stats_bytes, st));
+    u->prof_used = 0;
+    u->convs[0].in = x;
+    int rc;
+    for (const Op &op : u->ops) {
+        if (op.kind == 0) {
+            ConvLayer &c = u->convs[op.idx];
+            if ((rc = run_conv(u, c, batch, st))) return rc;
+            if (stop_layer && c.name == stop_layer) {
+                const int HW = c.Hout * c.Wout;
+                dim3 grid(std::min(ceil_div((long long)HW * c.cout, 256), kNumSMs * 8), batch);
+                if (u->plan.precision == TS2D_PREC_F32) nhwc_to_nchw_f32_kernel<float><<<grid, 256, 0, st>>>((const float *)c.norm_out, c.out_ps, c.cout, HW, debug_out);
+                else if (u->plan.precision == TS2D_PREC_BF16) nhwc_to_nchw_f32_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16 *)c.norm_out, c.out_ps, c.cout, HW, debug_out);
+                else nhwc_to_nchw_f32_kernel<__half><<<grid, 256, 0, st>>>((const __half *)c.norm_out, c.out_ps, c.cout, HW, debug_out);
+                TS2D_LAUNCH_CHECK();
+                u->last_batch = batch;
+                return TS2D_OK;
+            }
+        } else {
+            UpLayer &up = u->ups[op.idx];
+            if ((rc = run_up(u, up, batch, st))) return rc;
+            if (stop_layer && up.name == stop_layer) {
+                const int HW = up.Hin * up.sh * up.Win * up.sw;
+                dim3 grid(std::min(ceil_div((long long)HW * up.cout, 256), kNumSMs * 8), batch);
+                if (u->plan.precision == TS2D_PREC_F32) nhwc_to_nchw_f32_kernel<float><<<grid, 256, 0, st>>>((const float *)up.out, up.out_ps, up.cout, HW, debug_out);
+                else if (u->plan.precision == TS2D_PREC_BF16) nhwc_to_nchw_f32_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16 *)up.out, up.out_ps, up.cout, HW, debug_out);
+                else nhwc_to_nchw_f32_kernel<__half><<<grid, 256, 0, st>>>((const __half *)up.out, up.out_ps, up.cout, HW, debug_out);
+                TS2D_LAUNCH_CHECK();
+                u->last_batch = batch;
+                return TS2D_OK;
+            }
+        }
+    }
+    u->last_batch = batch;
+    if (stop_layer) { set_error("ts2d_unet_forward_debug: unknown layer '%s'", stop_layer); return TS2D_ERR_ARG; }
+    return TS2D_OK;
+}
+
+}  // namespace ts2d
+
+extern "C" int ts2d_unet_forward(ts2d_unet *u, const void *x_dev, int batch, ts2d_stream stream) {
+    TS2D_REQUIRE(u && x_dev, "ts2d_unet_forward: null pointer");
+    return forward_impl(u, x_dev, batch, nullptr, nullptr, (cudaStream_t)stream);
+}
+
+extern "C" int ts2d_unet_forward_debug(ts2d_unet *u, const void *x_dev, int batch, const char *layer, float *out_dev, ts2d_stream stream) {
+    TS2D_REQUIRE(u && x_dev && layer && out_dev, "ts2d_unet_forward_debug: null pointer");
+    return forward_impl(u, x_dev, batch, layer, out_dev, (cudaStream_t)stream);
+}
+
+extern "C" int ts2d_unet_tile_logits(ts2d_unet *u, int batch, float *logits_dev, ts2d_stream stream) {
+    TS2D_REQUIRE(u && logits_dev, "ts2d_unet_tile_logits: null pointer");
+    if (!u->finalized || batch < 1 || batch > u->last_batch) { set_error("ts2d_unet_tile_logits: no forward of >= %d images to read", batch); return TS2D_ERR_STATE; }
+    const int HW = u->plan.patch_h * u->plan.patch_w, F = u->C[0], heads = u->plan.num_heads;
+    dim3 grid(ceil_div(HW, 128), batch);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (u->plan.precision == TS2D_PREC_F32) tile_logits_kernel<float><<<grid, 128, 0, st>>>((const float *)u->features, F, u->head_w.dev, u->head_b.dev, heads, HW, logits_dev);
+    else if (u->plan.precision == TS2D_PREC_BF16) tile_logits_kernel<__nv_bfloat16><<<grid, 128, 0, st>>>((const __nv_bfloat16 *)u->features, F, u->head_w.dev, u->head_b.dev, heads, HW, logits_dev);
+    else tile_logits_kernel<__half><<<grid, 128, 0, st>>>((const __half *)u->features, F, u->head_w.dev, u->head_b.dev, heads, HW, logits_dev);
+    TS2D_LAUNCH_CHECK();
+    u->launches++;
+    return TS2D_OK;
+}
+
+template <typename T>
+static int launch_blend(const BlendParams &p, int F, cudaStream_t st) {
+    const long long npix = (long long)p.h * p.w;
+    const int grid = ceil_div(npix, 128);
+    const size_t smem = (size_t)(p.heads * F + p.heads) * sizeof(float);
+    switch (F) {
+        case 8: blend_head_kernel<T, 8><<<grid, 128, smem, st>>>(p); break;
+        case 16: blend_head_kernel<T, 16><<<grid, 128, smem, st>>>(p); break;
+        case 32: blend_head_kernel<T, 32><<<grid, 128, smem, st>>>(p); break;
+        case 64: blend_head_kernel<T, 64><<<grid, 128, smem, st>>>(p); break;
+        default: set_error("ts2d_unet_blend_head: features_per_stage[0] must be 8, 16, 32 or 64 (got %d)", F); return TS2D_ERR_UNSUPPORTED;
+    }
+    TS2D_LAUNCH_CHECK();
+    return TS2D_OK;
+}
+
+extern "C" int ts2d_unet_blend_head(ts2d_unet *u, const int *tile_yx_host, int T, int M, int mirror_mask, int pad_top, int pad_left, int h, int w,
+                                    const float *gaussian_dev, float *logits_dev, uint8_t *mask_dev, int H0, int W0, int h0, int w0, int ch_off,
+                                    int ch_total, uint8_t *present_dev, ts2d_stream stream) {
+    TS2D_REQUIRE(u && tile_yx_host && gaussian_dev, "ts2d_unet_blend_head: null pointer");
+    TS2D_REQUIRE(T >= 1 && T <= 64, "ts2d_unet_blend_head: T must be 1..64");
+    TS2D_REQUIRE(M == (mirror_mask == 3 ? 4 : (mirror_mask ? 2 : 1)), "ts2d_unet_blend_head: M does not match the mirror mask");
+    TS2D_REQUIRE(logits_dev || mask_dev, "ts2d_unet_blend_head: no output requested");
+    if (!u->finalized || T * M > u->last_batch) { set_error("ts2d_unet_blend_head: the last forward ran %d images, %d needed", u->last_batch, T * M); return TS2D_ERR_STATE; }
+    if (mask_dev)
+        TS2D_REQUIRE(h0 >= 0 && w0 >= 0 && h0 + h <= H0 && w0 + w <= W0 && ch_off >= 0 && ch_off + u->plan.num_heads <= ch_total,
+                     "ts2d_unet_blend_head: mask window out of range");
+    BlendParams p;
+    memset(&p, 0, sizeof(p));
+    p.feat = u->features; p.T = T; p.M = M; p.mirror_mask = mirror_mask; p.Ph = u->plan.patch_h; p.Pw = u->plan.patch_w;
+    for (int t = 0; t < T; ++t) { p.yx[t][0] = tile_yx_host[2 * t]; p.yx[t][1] = tile_yx_host[2 * t + 1]; }
+    p.pad_top = pad_top; p.pad_left = pad_left; p.h = h; p.w = w;
+    p.gauss = gaussian_dev; p.head_w = u->head_w.dev; p.head_b = u->head_b.dev; p.heads = u->plan.num_heads;
+    p.logits = logits_dev; p.mask = mask_dev; p.W0 = W0; p.h0 = h0; p.w0 = w0; p.ch_off = ch_off; p.ch_total = ch_total;
+    p.present = present_dev;
+    cudaStream_t st = (cudaStream_t)stream;
+    int rc;
+    if (u->plan.precision == TS2D_PREC_F32) rc = launch_blend<float>(p, u->C[0], st);
+    else if (u->plan.precision == TS2D_PREC_BF16) rc = launch_blend<__nv_bfloat16>(p, u->C[0], st);
+    else rc = launch_blend<__half>(p, u->C[0], st);
+    if (rc) return rc;
+    u->launches++;
+    return TS2D_OK;
+}
+
+extern "C" int ts2d_permute_channels(const uint8_t *src_dev, uint8_t *dst_dev, int64_t n_pix, int C, const int *perm_host, ts2d_stream stream) {
+    TS2D_REQUIRE(src_dev && dst_dev && perm_host && src_dev != dst_dev, "ts2d_permute_channels: bad pointers");
+    TS2D_REQUIRE(C >= 1 && C <= 256 && n_pix >= 0, "ts2d_permute_channels: C must be 1..256");
+    PermList pl;
+    pl.C = C;
+    for (int j = 0; j < C; ++j) {
+        TS2D_REQUIRE(perm_host[j] >= 0 && perm_host[j] < C, "ts2d_permute_channels: perm[%d] out of range", j);
+        pl.perm[j] = perm_host[j];
+    }
+    if (n_pix == 0) return TS2D_OK;
+    const int grid = (int)std::min<long long>(((long long)n_pix * C + 255) / 256, (long long)kNumSMs * 16);
+    permute_channels_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src_dev, dst_dev, n_pix, pl);
+    TS2D_LAUNCH_CHECK();
+    return TS2D_OK;
+}
+
+extern "C" int ts2d_unet_resize(ts2d_unet *u, int max_batch) {
+    TS2D_REQUIRE(u && max_batch >= 1, "ts2d_unet_resize: bad arguments");
+    if (u->finalized && u->plan.max_batch == max_batch) return TS2D_OK;
+    u->plan.max_batch = max_batch;
+    return ts2d_unet_finalize(u);
+}
+
+extern "C" int ts2d_unet_set_profiling(ts2d_unet *u, int enable) {
+    TS2D_REQUIRE(u, "ts2d_unet_set_profiling: null handle");
+    u->profiling = enable != 0;
+    u->prof_used = 0;
+    return TS2D_OK;
+}
+
+extern "C" double ts2d_unet_last_conv_ms(ts2d_unet *u) {
+    if (!u || !u->profiling) return -1.0;
+    double total = 0.0;
+    for (int i = 0; i < u->prof_used; ++i) {
+        if (cudaEventSynchronize(u->prof_events[i].second) != cudaSuccess) return -1.0;
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, u->prof_events[i].first, u->prof_events[i].second) != cudaSuccess) return -1.0;
+        total += ms;
+    }
+    return total;
+}
+
+extern "C" int ts2d_unet_destroy(ts2d_unet *u) {
+    if (!u) return TS2D_OK;
+    auto fr = [](void *p) { if (p) cudaFree(p); };
+    for (auto &c : u->convs) { fr(c.w_direct); fr(c.w_tc); fr(c.b.dev); fr(c.gamma.dev); fr(c.beta.dev); }
+    for (auto &up : u->ups) { fr(up.w_direct); fr(up.w_tc); fr(up.b.dev); }
+    fr(u->head_w.dev); fr(u->head_b.dev); fr(u->arena);
+    for (auto &e : u->prof_events) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
+    delete u;
+    return TS2D_OK;
+}

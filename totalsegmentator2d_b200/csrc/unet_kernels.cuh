@@ -1,0 +1,254 @@
+// CUDA-core kernels of the U-Net engine: direct convolution (parity lock / first layer / odd shapes),
+// InstanceNorm-apply + LeakyReLU, and the fused mirror-average + Gaussian blend + 1x1 head + threshold kernel.
+//
+// Reference: dynamic_network_architectures ConvDropoutNormReLU / UNetDecoder as reached from
+// ts2d/core/inference/nnu.py:149-166; blending = nnUNetPredictor._internal_predict_sliding_window_return_logits
+// and export = export_prediction_from_logits (prediction_worker.py:209,215-221).
+#pragma once
+#include "common.cuh"
+
+namespace ts2d {
+
+// ------------------------------------------------------------------------------------------------------
+// Direct convolution, NHWC, fp32 accumulate.  Block = 128 threads = 32 pixels (lanes) x 4 warps of 8 output
+// channels; each block walks `pix_iters` groups of 32 pixels so that the InstanceNorm statistics leave the
+// block as 2*8 double atomics per warp.  Weights [tap][Cin][Cout] fp32 (warp-uniform loads).
+// Also used for transposed conv (k == stride): one launch per (dy,dx) with a 1x1 weight slice and the
+// scatter (y*my+dy, x*mx+dx).
+// ------------------------------------------------------------------------------------------------------
+struct DirectConvParams {
+    const void *in; long long in_ps; int Hin, Win, Cin;
+    const float *w; const float *bias;
+    void *out; long long out_ps; int Hout, Wout, Cout;
+    int kh, kw, sh, sw, ph, pw;
+    int my, mx, dy, dx, Hfull, Wfull;
+    double *stats;     // [N][Cout][2] or null
+    int pix_iters;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(128) conv_direct_kernel(const DirectConvParams p) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int n = blockIdx.z;
+    const int co0 = blockIdx.y * 32 + warp * 8;
+    const int npix = p.Hout * p.Wout;
+    const T *in = reinterpret_cast<const T *>(p.in) + (long long)n * p.Hin * p.Win * p.in_ps;
+    T *out = reinterpret_cast<T *>(p.out);
+    float ssum[8], ssq[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { ssum[j] = 0.f; ssq[j] = 0.f; }
+    for (int it = 0; it < p.pix_iters; ++it) {
+        const int pix = (blockIdx.x * p.pix_iters + it) * 32 + lane;
+        const bool valid = pix < npix;
+        const int oy = valid ? pix / p.Wout : 0, ox = valid ? pix % p.Wout : 0;
+        float acc[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = (p.bias && co0 + j < p.Cout) ? __ldg(&p.bias[co0 + j]) : 0.f;
+        if (co0 < p.Cout) {
+            for (int r = 0; r < p.kh; ++r) {
+                const int iy = oy * p.sh + r - p.ph;
+                for (int s = 0; s < p.kw; ++s) {
+                    const int ix = ox * p.sw + s - p.pw;
+                    const bool inb = valid && iy >= 0 && iy < p.Hin && ix >= 0 && ix < p.Win;
+                    const T *ip = in + ((long long)iy * p.Win + ix) * p.in_ps;
+                    const float *wp = p.w + (long long)(r * p.kw + s) * p.Cin * p.Cout + co0;
+                    for (int ci = 0; ci < p.Cin; ++ci) {
+                        const float x = inb ? to_f32<T>(ip[ci]) : 0.f;
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float wv = (co0 + j < p.Cout) ? __ldg(wp + (long long)ci * p.Cout + j) : 0.f;
+                            acc[j] = fmaf(x, wv, acc[j]);
+                        }
+                    }
+                }
+            }
+        }
+        if (valid) {
+            T *op = out + (((long long)n * p.Hfull + (long long)oy * p.my + p.dy) * p.Wfull + (long long)ox * p.mx + p.dx) * p.out_ps + co0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if (co0 + j < p.Cout) {
+                    const T r = from_f32<T>(acc[j]);
+                    op[j] = r;
+                    const float rf = to_f32<T>(r);
+                    ssum[j] += rf; ssq[j] += rf * rf;
+                }
+            }
+        }
+    }
+    if (p.stats) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float a = warp_sum(ssum[j]), b = warp_sum(ssq[j]);
+            if (lane == 0 && co0 + j < p.Cout) {
+                double *s = p.stats + ((long long)n * p.Cout + co0 + j) * 2;
+                atomicAdd(s, (double)a);
+                atomicAdd(s + 1, (double)b);
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// InstanceNorm2d(affine, biased variance over H*W per (n,c)) + LeakyReLU, from the epilogue statistics.
+// raw: dense [N][HW][C]; out: [N][HW] pixels with stride out_ps (may be a channel slice of a concat buffer).
+// ------------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) norm_act_kernel(const T *raw, const double *stats, const float *gamma, const float *beta, T *out,
+                                                       long long out_ps, int HW, int C, float eps, float slope, int pix_per_block) {
+    extern __shared__ float s_ss[];    // scale[C], shift[C]
+    const int n = blockIdx.y;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        const double mean = stats[((long long)n * C + c) * 2] / (double)HW;
+        const double var = fmax(stats[((long long)n * C + c) * 2 + 1] / (double)HW - mean * mean, 0.0);
+        const double rstd = 1.0 / sqrt(var + (double)eps);
+        const float g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
+        const float sc = (float)(rstd * (double)g);
+        s_ss[c] = sc;
+        s_ss[C + c] = (float)((double)b - mean * rstd * (double)g);
+    }
+    __syncthreads();
+    const long long p0 = (long long)blockIdx.x * pix_per_block;
+    const long long p1 = min((long long)HW, p0 + pix_per_block);
+    const T *src = raw + ((long long)n * HW) * C;
+    T *dst = out + ((long long)n * HW) * out_ps;
+    if constexpr (sizeof(T) == 2) {
+        if ((C & 7) == 0 && (out_ps & 7) == 0) {
+            const int cv = C >> 3;
+            for (long long i = p0 * cv + threadIdx.x; i < p1 * cv; i += blockDim.x) {
+                const long long pix = i / cv;
+                const int c0 = (int)(i % cv) * 8;
+                uint4 v = *reinterpret_cast<const uint4 *>(src + pix * C + c0);
+                T *e = reinterpret_cast<T *>(&v);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    float y = fmaf(to_f32<T>(e[j]), s_ss[c0 + j], s_ss[C + c0 + j]);
+                    y = y > 0.f ? y : y * slope;
+                    e[j] = from_f32<T>(y);
+                }
+                *reinterpret_cast<uint4 *>(dst + pix * out_ps + c0) = v;
+            }
+            return;
+        }
+    }
+    for (long long i = p0 * C + threadIdx.x; i < p1 * C; i += blockDim.x) {
+        const long long pix = i / C;
+        const int c = (int)(i % C);
+        float y = fmaf(to_f32<T>(src[i]), s_ss[c], s_ss[C + c]);
+        y = y > 0.f ? y : y * slope;
+        dst[pix * out_ps + c] = from_f32<T>(y);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// Fused: mirror-TTA average + Gaussian-weighted tile blend + 1x1 segmentation head + (logits | threshold+paste).
+// The head is linear, so  sum_t g_t (W f_t + b) / sum_t g_t  ==  W (sum_t g_t f_t / sum_t g_t) + b : the F-channel
+// decoder features are blended and the head applied once per output pixel.  One thread per output pixel.
+// feat: [T*M][Ph][Pw][F] normalised+activated features of the last decoder conv.
+// ------------------------------------------------------------------------------------------------------
+struct BlendParams {
+    const void *feat; int T, M, mirror_mask; int Ph, Pw;
+    int yx[64][2];
+    int pad_top, pad_left, h, w;
+    const float *gauss;        // [Ph][Pw]
+    const float *head_w;       // [heads][F]
+    const float *head_b;       // [heads]
+    int heads;
+    float *logits;             // [heads][h][w] or null
+    uint8_t *mask;             // [H0][W0][ch_total] or null
+    int W0, h0, w0, ch_off, ch_total;
+    uint8_t *present;          // [ch_total] or null
+};
+
+template <typename T, int F>
+__global__ void __launch_bounds__(128) blend_head_kernel(const BlendParams p) {
+    extern __shared__ float s_head[];            // head_w [heads][F] then head_b[heads]
+    for (int i = threadIdx.x; i < p.heads * F; i += blockDim.x) s_head[i] = p.head_w[i];
+    for (int i = threadIdx.x; i < p.heads; i += blockDim.x) s_head[p.heads * F + i] = p.head_b ? p.head_b[i] : 0.f;
+    __syncthreads();
+    const long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix >= (long long)p.h * p.w) return;
+    const int y = (int)(pix / p.w), x = (int)(pix % p.w);
+    const int yp = y + p.pad_top, xp = x + p.pad_left;
+    float acc[F];
+#pragma unroll
+    for (int k = 0; k < F; ++k) acc[k] = 0.f;
+    float wsum = 0.f;
+    const T *feat = reinterpret_cast<const T *>(p.feat);
+    const float inv_m = 1.0f / (float)p.M;
+    for (int t = 0; t < p.T; ++t) {
+        const int ly = yp - p.yx[t][0], lx = xp - p.yx[t][1];
+        if (ly < 0 || ly >= p.Ph || lx < 0 || lx >= p.Pw) continue;
+        const float g = p.gauss[ly * p.Pw + lx];
+        wsum += g;
+        const float gm = g * inv_m;
+        for (int m = 0; m < p.M; ++m) {
+            bool fh = false, fw = false;
+            if (p.mirror_mask == 3) { fh = (m == 1 || m == 3); fw = (m == 2 || m == 3); }
+            else if (p.mirror_mask == 1) fh = (m == 1);
+            else if (p.mirror_mask == 2) fw = (m == 1);
+            const int sy = fh ? p.Ph - 1 - ly : ly, sx = fw ? p.Pw - 1 - lx : lx;
+            const T *f = feat + (((long long)(t * p.M + m) * p.Ph + sy) * p.Pw + sx) * F;
+            if constexpr (sizeof(T) == 2 && (F % 8) == 0) {
+#pragma unroll
+                for (int k = 0; k < F; k += 8) {
+                    uint4 v = *reinterpret_cast<const uint4 *>(f + k);
+                    const T *e = reinterpret_cast<const T *>(&v);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) acc[k + j] = fmaf(gm, to_f32<T>(e[j]), acc[k + j]);
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < F; ++k) acc[k] = fmaf(gm, to_f32<T>(f[k]), acc[k]);
+            }
+        }
+    }
+    const float inv = 1.0f / wsum;
+#pragma unroll
+    for (int k = 0; k < F; ++k) acc[k] *= inv;
+    for (int c = 0; c < p.heads; ++c) {
+        float v = s_head[p.heads * F + c];
+#pragma unroll
+        for (int k = 0; k < F; ++k) v = fmaf(s_head[c * F + k], acc[k], v);
+        if (p.logits) p.logits[((long long)c * p.h + y) * p.w + x] = v;
+        if (p.mask) p.mask[((long long)(p.h0 + y) * p.W0 + (p.w0 + x)) * p.ch_total + p.ch_off + c] = v > 0.f ? 1 : 0;
+        if (p.present && v > 0.f) p.present[p.ch_off + c] = 1;
+    }
+}
+
+// per-image head (inspection): feat [N][HW][F] -> logits [N][heads][HW]
+template <typename T>
+__global__ void __launch_bounds__(128) tile_logits_kernel(const T *feat, int F, const float *head_w, const float *head_b, int heads, int HW, float *logits) {
+    const int n = blockIdx.y;
+    const long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix >= HW) return;
+    const T *f = feat + ((long long)n * HW + pix) * F;
+    for (int c = 0; c < heads; ++c) {
+        float v = head_b ? head_b[c] : 0.f;
+        for (int k = 0; k < F; ++k) v = fmaf(head_w[c * F + k], to_f32<T>(f[k]), v);
+        logits[((long long)n * heads + c) * HW + pix] = v;
+    }
+}
+
+// dst[pix][j] = src[pix][perm[j]]
+struct PermList { int C; int perm[256]; };
+__global__ void __launch_bounds__(256) permute_channels_kernel(const uint8_t *src, uint8_t *dst, long long n, PermList pl) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n * pl.C; i += (long long)gridDim.x * blockDim.x) {
+        const long long pix = i / pl.C;
+        const int j = (int)(i % pl.C);
+        dst[i] = src[pix * pl.C + pl.perm[j]];
+    }
+}
+
+// NHWC (pixel stride ps) -> float32 NCHW (layer-wise parity tests)
+template <typename T>
+__global__ void __launch_bounds__(256) nhwc_to_nchw_f32_kernel(const T *in, long long ps, int C, int HW, float *out) {
+    const int n = blockIdx.y;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < (long long)HW * C; i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i / HW);
+        const long long pix = i % HW;
+        out[((long long)n * C + c) * HW + pix] = to_f32<T>(in[((long long)n * HW + pix) * ps + c]);
+    }
+}
+
+}  // namespace ts2d

@@ -1,0 +1,137 @@
+"""Thin torch-tensor wrappers over the C ABI (one function per entry point).
+
+PyTorch is plumbing here: it allocates device memory and provides the stream; the
+arithmetic is in libts2d_b200.so.  Each wrapper cites the reference call it replaces.
+"""
+from __future__ import annotations
+
+from typing import Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import _lib as L
+
+_NP_TO_TS = {np.dtype("uint8"): L.U8, np.dtype("int16"): L.I16, np.dtype("uint16"): L.U16, np.dtype("int32"): L.I32,
+             np.dtype("float32"): L.F32, np.dtype("float64"): L.F64}
+_TORCH_TO_TS = {torch.uint8: L.U8, torch.int16: L.I16, torch.uint16: L.U16, torch.int32: L.I32, torch.float32: L.F32,
+                torch.float64: L.F64}
+_PREC_TO_TORCH = {L.PREC_F32: torch.float32, L.PREC_BF16: torch.bfloat16, L.PREC_F16: torch.float16}
+_MODE_IDS = {"mean": L.PROJ_MEAN, "avg": L.PROJ_MEAN, "max": L.PROJ_MAX, "mip": L.PROJ_MAX, "min": L.PROJ_MIN}
+
+
+def _dev(t: torch.Tensor, what: str):
+    if not t.is_cuda or not t.is_contiguous():
+        raise L.TS2DError(f"{what} must be a contiguous CUDA tensor")
+    return t.data_ptr()
+
+
+def project(vol: torch.Tensor, modes: Sequence[str], reduce_dim: int = 1, h_dim: int = 0, flip_h: bool = False,
+            flip_w: bool = False, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """K1. vol: CUDA tensor [n0][n1][n2]; returns float32 [len(modes)][H][W].
+    Replaces reorient_image + project + Cast + Compose (reference ts2d/core/util/image.py:32-101, ts2d/tool.py:154-160,181-185)."""
+    lib = L.load()
+    if vol.dim() != 3:
+        raise L.TS2DError("project expects a 3-D volume")
+    if vol.dtype not in _TORCH_TO_TS:
+        raise L.TS2DError(f"unsupported voxel type {vol.dtype}")
+    ids = []
+    for m in modes:
+        key = str(m).lower().strip()
+        if key not in _MODE_IDS:
+            raise RuntimeError("Unsupported filter mode: {}".format(key))
+        ids.append(_MODE_IDS[key])
+    kept = [d for d in range(3) if d != reduce_dim]
+    w_dim = kept[0] if kept[1] == h_dim else kept[1]
+    H, W = int(vol.shape[h_dim]), int(vol.shape[w_dim])
+    if out is None:
+        out = torch.empty((len(ids), H, W), dtype=torch.float32, device=vol.device)
+    L.check(lib.ts2d_project(_dev(vol, "vol"), _TORCH_TO_TS[vol.dtype], vol.shape[0], vol.shape[1], vol.shape[2], reduce_dim, h_dim,
+                             int(flip_h), int(flip_w), L.int_array(ids), len(ids), _dev(out, "out"), L.stream_ptr()), "ts2d_project")
+    return out
+
+
+def bbox_nonzero(img: torch.Tensor) -> torch.Tensor:
+    """crop_to_nonzero bbox (nnunetv2 cropping.py) -> int32[4] device tensor {h0,h1,w0,w1}."""
+    lib = L.load()
+    C, H, W = img.shape
+    out = torch.empty(4, dtype=torch.int32, device=img.device)
+    L.check(lib.ts2d_bbox_nonzero(_dev(img, "img"), C, H, W, out.data_ptr(), L.stream_ptr()), "ts2d_bbox_nonzero")
+    return out
+
+
+def channel_stats(img: torch.Tensor, bbox: Tuple[int, int, int, int]) -> torch.Tensor:
+    lib = L.load()
+    C, H, W = img.shape
+    out = torch.empty((C, 4), dtype=torch.float64, device=img.device)
+    L.check(lib.ts2d_channel_stats(_dev(img, "img"), C, H, W, *[int(b) for b in bbox], out.data_ptr(), L.stream_ptr()), "ts2d_channel_stats")
+    return out
+
+
+def normalize(img: torch.Tensor, bbox, schemes: Sequence[int], params: Optional[Sequence[Sequence[float]]], stats: Optional[torch.Tensor]) -> torch.Tensor:
+    """DefaultPreprocessor._normalize on the cropped image (nnunetv2 default_normalization_schemes.py)."""
+    lib = L.load()
+    C, H, W = img.shape
+    h0, h1, w0, w1 = [int(b) for b in bbox]
+    out = torch.empty((C, h1 - h0, w1 - w0), dtype=torch.float32, device=img.device)
+    flat = None
+    if params is not None:
+        flat = L.float_array([v for row in params for v in row])
+    L.check(lib.ts2d_normalize(_dev(img, "img"), C, H, W, h0, h1, w0, w1, L.int_array(list(schemes)), flat,
+                               stats.data_ptr() if stats is not None else None, out.data_ptr(), L.stream_ptr()), "ts2d_normalize")
+    return out
+
+
+def resample2d(img: torch.Tensor, new_hw: Sequence[int], order: int) -> torch.Tensor:
+    """skimage.transform.resize(order, mode='edge', anti_aliasing=False) per channel (nnunetv2 default_resampling.py)."""
+    lib = L.load()
+    C, h, w = img.shape
+    h2, w2 = int(new_hw[0]), int(new_hw[1])
+    out = torch.empty((C, h2, w2), dtype=torch.float32, device=img.device)
+    scratch = None
+    if order == 3:
+        scratch = torch.empty(C * (h + 24) * (w + 24) + 2 * C, dtype=torch.float64, device=img.device)
+    L.check(lib.ts2d_resample2d(_dev(img, "img"), C, h, w, out.data_ptr(), h2, w2, order,
+                                scratch.data_ptr() if scratch is not None else None, L.stream_ptr()), "ts2d_resample2d")
+    return out
+
+
+def mirror_count(mirror_mask: int) -> int:
+    return 4 if mirror_mask == 3 else (2 if mirror_mask else 1)
+
+
+def extract_tiles(img: torch.Tensor, pads: Tuple[int, int], patch: Sequence[int], tile_yx: Sequence[Tuple[int, int]], mirror_mask: int,
+                  precision: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """pad_nd_image + slicing + torch.flip of predict_sliding_window_return_logits -> NHWC tiles [T*M][Ph][Pw][C]."""
+    lib = L.load()
+    C, h, w = img.shape
+    T, M = len(tile_yx), mirror_count(mirror_mask)
+    if out is None:
+        out = torch.empty((T * M, int(patch[0]), int(patch[1]), C), dtype=_PREC_TO_TORCH[precision], device=img.device)
+    flat = [v for yx in tile_yx for v in yx]
+    L.check(lib.ts2d_extract_tiles(_dev(img, "img"), C, h, w, int(pads[0]), int(pads[1]), int(patch[0]), int(patch[1]), L.int_array(flat), T,
+                                   mirror_mask, precision, out.data_ptr(), L.stream_ptr()), "ts2d_extract_tiles")
+    return out
+
+
+def threshold_logits(logits: torch.Tensor, new_hw, mask: torch.Tensor, h0: int, w0: int, ch_off: int):
+    """export_prediction_from_logits for a resampling plan: order-1 resize -> sigmoid>0.5 -> paste."""
+    lib = L.load()
+    heads, h, w = logits.shape
+    H0, W0, ch_total = mask.shape
+    L.check(lib.ts2d_threshold_logits(_dev(logits, "logits"), heads, h, w, int(new_hw[0]), int(new_hw[1]), _dev(mask, "mask"), H0, W0, h0, w0,
+                                      ch_off, ch_total, L.stream_ptr()), "ts2d_threshold_logits")
+
+
+def permute_channels(src: torch.Tensor, perm: Sequence[int], out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    lib = L.load()
+    Cc = src.shape[-1]
+    if out is None:
+        out = torch.empty_like(src)
+    L.check(lib.ts2d_permute_channels(_dev(src, "src"), _dev(out, "out"), src.numel() // Cc, Cc, L.int_array(list(perm)), L.stream_ptr()),
+            "ts2d_permute_channels")
+    return out
+
+
+def torch_dtype_of(precision: int):
+    return _PREC_TO_TORCH[precision]

@@ -1,0 +1,323 @@
+"""Public API: ``TS2D(key).predict(input) -> TS2D.Result`` / ``Result.save(...)``.
+
+Drop-in for reference ts2d/tool.py:19-311 (same constructor, context manager, ``predict`` signature, result
+dictionary keys, ``Result`` accessors, ``save`` arguments, file naming and error messages).  What changed is
+underneath: the volume is uploaded once, reoriented + projected by one kernel (instead of DICOMOrient per model
+and one ITK filter per channel, tool.py:154-159), preprocessed once for all models that share a plan, and the
+five group models write straight into one merged mask in HBM (instead of five subprocess round trips through
+gzip-NRRD temp files and 117 SimpleITK calls in combine_segmentations, image.py:490-510).
+"""
+from __future__ import annotations
+
+import os
+import traceback
+from typing import Dict, List, Optional
+
+import numpy as np
+import torch
+
+from . import _lib as L
+from . import ops
+from .core.inference.database import decompose_model_key
+from .core.inference.nnu import NNUDeviceModel, NNUModel
+from .core.inference.zoo import NNUZoo
+from .core.util.config import get_label_colors
+from .core.util.image import (_projected_image, _reoriented_geometry, _to_device, axis_name_to_index, combine_segmentations, compose,
+                              get_actual_dimension, merge_order, orientation_remap, read_image, reduce_dimensions, split_channels)
+from .core.util.log import log, warn
+from .core.util.meta import copy_image_geo, copy_image_meta, set_annotation_meta
+from .image import Image, from_sitk
+from .nrrd import write_nrrd
+
+
+def _as_list(v):
+    if v is None:
+        return []
+    return list(v) if isinstance(v, (list, tuple, set)) else [v]
+
+
+class _LazySeg:
+    """per-model segmentation that is still in HBM; ``Result.get_segmentation(model)`` brings it to the host"""
+
+    def __init__(self, mask_dev: torch.Tensor, lo: int, hi: int, finish):
+        self.mask_dev, self.lo, self.hi, self.finish = mask_dev, lo, hi, finish
+        self._img: Optional[Image] = None
+
+    def materialize(self) -> Image:
+        if self._img is None:
+            arr = self.mask_dev[..., self.lo:self.hi].contiguous().cpu().numpy()
+            self._img = self.finish(arr)
+            self.mask_dev = None
+        return self._img
+
+
+class TS2D:
+    def __init__(self, key: str = "ts2d", use_remote: bool = True, fetch_remote: bool = True, models_root: Optional[str] = None,
+                 param: Optional[dict] = None):
+        """
+        :param key: the model key to use, defaults to "ts2d"
+        :param use_remote / fetch_remote: accepted for compatibility; models are resolved from the local database only
+               (``~/.ts2d/models`` or ``$TS2D_MODELS``) because downloading is outside the accelerated path
+        :param models_root: overrides the local database root
+        :param param: extra ``nnu.*`` / ``b200.*`` parameters merged over each model.json
+        """
+        colors = get_label_colors()
+        p = {"server.workers": 1, "nnu.result.colors": colors}
+        p.update(param or {})
+        L.load(check_device=True)       # fail loudly: no CPU fallback
+        self.zoo = NNUZoo(remote=False, root=models_root)
+        self.models: Dict[str, NNUDeviceModel] = dict()
+        ids = self.zoo.resolve(key, unique_model=True)
+        if not ids:
+            raise RuntimeError(f"No models were resolved for key: {key}")
+        if len(ids) > 1:
+            log(f"The model key '{key}' was resolved to {len(ids)} models: {', '.join(ids)}.")
+        for id in ids:
+            try:
+                model = self.zoo.load(id, interface="process", param=p)
+                model.start(wait=False)
+                if not model.multilabel:
+                    warn(f"The loaded model {id} is not configured for multilabel inference - this should not be the case in TS2D and may lead to unexpected results.")
+                self.models[id] = model
+            except Exception:
+                traceback.print_exc()
+                raise RuntimeError(f"Failed to load model {id}" + (f" (resolved from {key})" if key != id else ""))
+        for model in self.models.values():
+            model.await_startup()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, exc_type, exc_val, exc_tb):
+        self.close()
+
+    def close(self):
+        for model in self.models.values():
+            model.stop()
+        self.models = dict()
+
+    def __del__(self):
+        try:
+            if getattr(self, "models", None):
+                self.close()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------------------------------------
+    def predict(self, input, collapse: bool = False, merge: bool = True):
+        """
+        Predict the segmentation for the given input image.
+        :param input: the input image (Image / sitk.Image) or a path to an image file
+        :param collapse: collapse the output image and segmentation to 2D (discards the 3D orientation)
+        :param merge: merge the individual model segmentations into a single segmentation image
+        """
+        if isinstance(input, str):
+            input = read_image(input)
+        try:
+            input = from_sitk(input)
+        except RuntimeError:
+            raise RuntimeError(f"input must be a string path or a SimpleITK image, found: {type(input).__name__}")
+
+        ids = list(self.models.keys())
+        is3d = get_actual_dimension(input) > 2
+        chan_defs = dict()
+        for id in ids:
+            ch = self.models[id].channels
+            if ch is None:
+                raise RuntimeError(f"Model {id} does not have a channel definition, cannot project the input image.")
+            chan_defs[id] = sorted(ch.items(), key=lambda x: x[0])
+
+        result = dict()
+        projections: Dict[str, Image] = dict()
+        proj_dev: Dict[str, torch.Tensor] = dict()
+        if is3d:
+            # one pass: reorient (folded into addressing) + every projection any model asks for
+            names = []
+            for id in ids:
+                for _, n in chan_defs[id]:
+                    if n not in names:
+                        names.append(n)
+            perm, flip = orientation_remap(input.direction_matrix(), "RAI")
+            size, sp, org, nd = _reoriented_geometry(input, perm, flip)
+            vol = _to_device(input.array)
+            ax = axis_name_to_index("coronal")
+            out = ops.project(vol, names, reduce_dim=2 - perm[ax], h_dim=2 - perm[2], flip_h=flip[2], flip_w=flip[0])
+            del vol
+            host = out.cpu().numpy()
+            for i, n in enumerate(names):
+                projections[n] = _projected_image(host[i], size, sp, org, nd, ax)
+                proj_dev[n] = out[i]
+            spacing_xy = (sp[0], sp[2])
+            H, W = int(out.shape[1]), int(out.shape[2])
+            geo3d = projections[names[0]]
+        else:
+            base2d = input if input.GetDimension() < 3 else reduce_dimensions(input)
+            chs = split_channels(input)
+            projections.update((f"ch{i}", ch) for i, ch in enumerate(chs))
+            arr = np.asarray(base2d.array, dtype=np.float32)
+            chw = np.moveaxis(arr, -1, 0) if base2d.is_vector else arr[None]
+            img_dev_2d = torch.from_numpy(np.ascontiguousarray(chw)).cuda()
+            spacing_xy = base2d.GetSpacing()
+            H, W = int(chw.shape[1]), int(chw.shape[2])
+
+        heads = [self.models[id].predictor.num_heads for id in ids]
+        offs = np.concatenate([[0], np.cumsum(heads)]).astype(int)
+        total = int(offs[-1])
+        mask = torch.zeros((H, W, total), dtype=torch.uint8, device="cuda")
+        present = torch.zeros(total, dtype=torch.uint8, device="cuda")
+        cache = dict()
+        model_inputs = dict()
+        for k, id in enumerate(ids):
+            model = self.models[id]
+            res = {"id": id, "revision": model.revision}
+            res["model"], res["group"] = decompose_model_key(id)
+            if is3d:
+                img_dev = torch.stack([proj_dev[n] for _, n in chan_defs[id]], dim=0)
+                ch_list = [projections[n] for _, n in chan_defs[id]]
+                minput = compose(ch_list) if len(ch_list) > 1 else ch_list[0]
+            else:
+                model_nch, input_nch = len(chan_defs[id]), input.GetNumberOfComponentsPerPixel()
+                if model_nch != input_nch:
+                    raise RuntimeError(f"The number of channels in the input image does not match the models channel definition ({model_nch} vs {input_nch}).")
+                img_dev, minput = img_dev_2d, input
+            try:
+                model.predict_device(img_dev, spacing_xy, mask=mask, ch_off=int(offs[k]), present=present, cache=cache)
+            except L.TS2DError as ex:
+                raise RuntimeError(f"Prediction failed for: {id} ({ex})") from ex
+            native_2d = minput.GetDimension() < 3
+            input2d = minput if native_2d else reduce_dimensions(minput)
+            model_inputs[id] = (minput, input2d, native_2d)
+            res["input"] = input2d if collapse else minput
+            result.setdefault("models", dict())[id] = res
+
+        def finisher(id):
+            minput, input2d, native_2d = model_inputs[id]
+
+            def fin(arr):
+                seg = Image(arr, input2d.GetSpacing(), input2d.GetOrigin(), input2d.GetDirection(), is_vector=True)
+                self.models[id].annotate(seg)
+                return seg if collapse or native_2d else self._restore_dimension(seg, minput)
+            return fin
+
+        for k, id in enumerate(ids):
+            result["models"][id]["segmentation"] = _LazySeg(mask, int(offs[k]), int(offs[k + 1]), finisher(id))
+
+        if merge:
+            if len(ids) == 1:
+                result["segmentation"] = result["models"][ids[0]]["segmentation"].materialize()
+            else:
+                # channel order of combine_segmentations (present labels first) applied on the device
+                pres = present.cpu().numpy().astype(bool)
+                perm, names, colors = [], dict(), dict()
+                for k, id in enumerate(ids):
+                    m = self.models[id]
+                    p = pres[offs[k]:offs[k + 1]]
+                    lab = m.label_names
+                    col = m.get_colors() or {}
+                    order = [c for c in range(len(lab)) if p[c]] + [c for c in range(len(lab)) if not p[c]]
+                    for c in order:
+                        names[len(perm) + 1] = lab[c]
+                        if col.get(lab[c]) is not None:
+                            colors[lab[c]] = col[lab[c]]
+                        perm.append(int(offs[k]) + c)
+                merged = ops.permute_channels(mask, perm).cpu().numpy()
+                minput, input2d, native_2d = model_inputs[ids[0]]
+                seg = Image(merged, input2d.GetSpacing(), input2d.GetOrigin(), input2d.GetDirection(), is_vector=True)
+                set_annotation_meta(seg, names=names, colors=colors)
+                result["segmentation"] = seg if collapse or native_2d else self._restore_dimension(seg, minput)
+
+        result["input"] = input
+        if projections:
+            result["projections"] = projections
+        return TS2D.Result(result)
+
+    @staticmethod
+    def _project(img: Image, mode: str) -> Image:
+        from .core.util.image import project
+        res = project(img, mode=mode, axis="coronal")
+        return Image(res.array.astype(np.float32), res.GetSpacing(), res.GetOrigin(), res.GetDirection())
+
+    @staticmethod
+    def _restore_dimension(img: Image, ref: Image) -> Image:
+        shape = list(reversed(ref.GetSize())) + [-1]
+        out = Image(np.reshape(img.array, shape), ref.GetSpacing(), ref.GetOrigin(), ref.GetDirection(), is_vector=True)
+        copy_image_meta(out, img)
+        return out
+
+    # ------------------------------------------------------------------------------------------------
+    class Result:
+        def __init__(self, data: dict):
+            self.data = data
+
+        @property
+        def models(self) -> List[str]:
+            return sorted(self.data.get("models", dict()).keys())
+
+        def get_input(self, model: Optional[str] = None):
+            if model is not None:
+                return self.data.get("models", dict()).get(model, dict()).get("input")
+            return self.data.get("input")
+
+        def get_segmentation(self, model: Optional[str] = None):
+            if model is not None:
+                entry = self.data.get("models", dict()).get(model, dict())
+                seg = entry.get("segmentation")
+                if isinstance(seg, _LazySeg):
+                    seg = seg.materialize()
+                    entry["segmentation"] = seg
+                return seg
+            return self.data.get("segmentation")
+
+        def get_projection(self, channel: Optional[str] = None):
+            projections = self.data.get("projections", dict())
+            if channel is not None:
+                return projections.get(channel)
+            return projections
+
+        def save(self, dest: str, name: str = "result", ext: str = "nrrd", models="final", targets="all", content: str = "all",
+                 naming: str = "group"):
+            assert ext.lower() != "png", "PNG is not a valid export format for the 'file' content type."
+            assert naming in {"group", "model"}, f"Invalid naming scheme '{naming}', must be one of 'group' or 'model'."
+            assert content in {"file", "visual", "all"}, f"Invalid export type '{content}', must be one of 'file', 'visual' or 'all'."
+            content = {"visual", "file"} if content == "all" else {content}
+            models = set(t.strip().lower() if isinstance(t, str) else t for t in _as_list(models))
+            if "all" in models:
+                models |= set(self.models) | {None}
+            if "final" in models:
+                models |= {None}
+            models -= {"all", "final"}
+            targets = set(t.strip().lower() for t in _as_list(targets))
+
+            def _make_filename(base, key):
+                if key is not None and naming == "group":
+                    _, group = decompose_model_key(key)
+                    return f"{base}-{group}"
+                return base if key is None else f"{base}-{key}"
+
+            def _write(img, filepath):
+                if ext.lower() != "nrrd":
+                    raise RuntimeError(f"unsupported export format '{ext}' (this build writes .nrrd)")
+                write_nrrd(img, filepath, True)
+
+            def _export_image(img, base_name, suffix="", labels=False):
+                if "file" in content:
+                    _write(img, os.path.join(dest, f"{base_name}{suffix}.{ext}"))
+                if "visual" in content:
+                    from .core.util.visual import write_visual
+                    write_visual(img, os.path.join(dest, base_name), suffix, labels)
+
+            os.makedirs(dest, exist_ok=True)
+            ordered = sorted(models, key=lambda k: (k is not None, str(k)))
+            if {"all", "input"} & targets:
+                for key in ordered:
+                    img = self.get_input(key)
+                    if img is not None:
+                        _export_image(img, _make_filename(name, key))
+            if {"all", "segmentation"} & targets:
+                for key in ordered:
+                    img = self.get_segmentation(key)
+                    if img is not None:
+                        _export_image(img, _make_filename(name, key), suffix=".seg", labels=True)
+            if {"all", "projection"} & targets:
+                for channel, img in self.get_projection().items():
+                    _export_image(img, f"{name}_{channel}")
