@@ -1,0 +1,449 @@
+#!/usr/bin/env python
+"""bench.py - CT studies/s of the 5-model ts2d-v2 pipeline on B200 (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]            # this repo's CUDA path
+    python bench.py --impl reference [--gpus N] [--steps K] ...    # CPU restatement of the reference path (host cores)
+
+Workload (N=1, BASELINE.json configs[3] per GPU / SURVEY.md section 8d config 4A): synthetic CT studies
+512 x 512 x 1000 int16 ([z][y][x], 524 MB each, larger than the 126 MB L2), 1.5 mm isotropic, five random-init
+CS-512 group models (heads 18/23/24/26/26 = 117 labels), tile_step_size 0.5 (3 tiles of 512^2 per model), mirror
+TTA as the reference defaults to (augment=True, reference ts2d/core/inference/wrapper.py:65).
+
+  value  whole-job studies/s with the volumes already resident in HBM (device events, max over ranks)
+  e2e    the same metric through the public API ``TS2D.predict(Image)`` + ``Result.get_segmentation()`` with HOST
+         buffers: H2D of the int16 volume and D2H of the merged 117-channel mask inside the timed region
+  roofline       dominant kernel = the tcgen05 implicit-GEMM conv: algorithmic conv FLOPs / conv kernel time
+  roofline_hbm   the projection kernel against measured HBM bandwidth
+  cpu_baseline   the oracle (CPU restatement of SimpleITK + nnU-Net + torch-CPU) timed on this host's cores
+
+One process per GPU; under torchrun each rank processes its own studies (no data-path collective, weak scaling).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np
+import torch
+
+METRIC = "ct_studies_per_sec_5model_ts2d_v2"
+UNIT = "studies/s"
+VOL_SHAPE = (1000, 512, 512)           # [z][y][x]
+SPACING = (1.5, 1.5, 1.5)
+MODEL_KEY = "ts2d-v2-ep4000b2"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--studies-per-step", type=int, default=2, help="studies each rank processes per step")
+    ap.add_argument("--precision", default=os.environ.get("TS2D_BENCH_PRECISION", "bf16"), choices=["bf16", "fp16"])
+    ap.add_argument("--mirror", type=int, default=1, help="1: mirror TTA on (reference default), 0: off")
+    ap.add_argument("--small", action="store_true", help="tiny shapes (debugging only; the JSON line says so)")
+    ap.add_argument("--skip-cpu", action="store_true", help="omit the cpu_baseline leg")
+    ap.add_argument("--skip-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def load_peaks():
+    fallback = {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return {"hbm_gbs": float(p["hbm_gbs"]), "bf16_tflops": float(p["bf16_tflops"]),
+                "bf16_tflops_sustained": float(p.get("bf16_tflops_sustained", p["bf16_tflops"]))}, "measured"
+    except Exception:
+        return fallback, "fallback"
+
+
+def synthetic_volume(seed: int, shape=VOL_SHAPE) -> np.ndarray:
+    """clip(round(N(-300, 450)), -1024, 3071) + centred ellipsoid body N(300, 200); int16 [z][y][x].
+    Generated slab-wise in float32 to bound host memory."""
+    rng = np.random.default_rng(seed)
+    nz, ny, nx = shape
+    vol = np.empty(shape, dtype=np.int16)
+    yy, xx = np.ogrid[:ny, :nx]
+    ey = ((yy - ny / 2) / (0.35 * ny)) ** 2 + ((xx - nx / 2) / (0.4 * nx)) ** 2
+    for z0 in range(0, nz, 50):
+        z1 = min(nz, z0 + 50)
+        air = rng.standard_normal((z1 - z0, ny, nx), dtype=np.float32) * 450.0 - 300.0
+        body = rng.standard_normal((z1 - z0, ny, nx), dtype=np.float32) * 200.0 + 300.0
+        zz = ((np.arange(z0, z1)[:, None, None] - nz / 2) / (0.4 * nz)) ** 2
+        inside = (zz + ey[None]) < 1.0
+        vol[z0:z1] = np.clip(np.round(np.where(inside, body, air)), -1024, 3071).astype(np.int16)
+    return vol
+
+
+def write_zoo(root: str, small: bool, mirror: bool, only=None):
+    """returns (all five groups, patch); ``only`` restricts which model directories are written (seeds unchanged)"""
+    from totalsegmentator2d_b200 import synth
+    if small:
+        arch = synth.make_arch_kwargs([32, 64, 128, 128])
+        groups = {g: labels[:4 + i] for i, (g, labels) in enumerate(synth.TS2D_V2_GROUPS.items())}
+        patch = (128, 128)
+    else:
+        arch, groups, patch = synth.cs512_arch(), synth.TS2D_V2_GROUPS, (512, 512)
+    for gi, (g, labels) in enumerate(groups.items()):
+        if only is None or g in only:
+            synth.write_model_dir(root, MODEL_KEY, g, labels, arch, patch, (1.5, 1.5), seed=1000 + gi, mirror_axes=(0, 1) if mirror else None)
+    return groups, patch
+
+
+class ClockSampler:
+    """nvidia-smi clock / throttle-reason samples DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], None, [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx = float(f[1]); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "power_w_max": max(pw) if pw else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ----------------------------------------------------------------------------------------------------------
+# CPU leg: the oracle (restatement of the reference's SimpleITK + nnU-Net + torch-CPU path) on the host cores
+# ----------------------------------------------------------------------------------------------------------
+class CpuReference:
+    """Times the reference path per stage on a BOUNDED sample of the workload and scales to one study:
+    projection (C/OpenMP restatement of the two ITK filters, full volume) + preprocessing (full image) +
+    sliding-window U-Net of ONE tile (of T) with its mirror passes for ONE model (of 5) + export (full image,
+    one model).  study_seconds = t_proj + n_models * (t_pre + T * t_tile + t_export)."""
+
+    def __init__(self, zoo_root: str, groups, mirror: bool):
+        import ctypes
+        from oracle import pipeline as opipe
+        self.opipe = opipe
+        self.mirror = mirror
+        self.groups = list(groups)
+        torch.set_num_threads(os.cpu_count() or 1)
+        self.cores = torch.get_num_threads()
+        g = "ribs" if "ribs" in self.groups else self.groups[0]
+        self.model = opipe.OracleModel(opipe.find_training_dir(os.path.join(zoo_root, f"{MODEL_KEY}_{g}", "r001")))
+        so = os.path.join(ROOT, "oracle", "liboracle_projection.so")
+        self.clib = ctypes.CDLL(so) if os.path.exists(so) else None
+
+    def project(self, vol: np.ndarray) -> np.ndarray:
+        import ctypes
+        nz, ny, nx = vol.shape
+        out = np.empty((2, nz, nx), dtype=np.float32)
+        if self.clib is not None and vol.dtype == np.int16:
+            for i, fn in enumerate((self.clib.oracle_project_mean_i16, self.clib.oracle_project_max_i16)):
+                fn.restype = None
+                fn(vol.ctypes.data_as(ctypes.c_void_p), ctypes.c_int64(nz), ctypes.c_int64(ny), ctypes.c_int64(nx),
+                   out[i].ctypes.data_as(ctypes.c_void_p))
+            return out
+        from oracle import geometry
+        return geometry.project_channels(vol, ["mean", "max"])
+
+    def sample(self, vol: np.ndarray) -> dict:
+        from oracle import nnunet_inf, nnunet_pre
+        m = self.model
+        t0 = time.perf_counter()
+        img = self.project(vol)
+        t1 = time.perf_counter()
+        with torch.no_grad():
+            sp = nnunet_pre.sitkio_spacing_2d((SPACING[0], SPACING[2]))
+            pre, props = nnunet_pre.run_case_npy(img[:, None], sp, m.spacing, m.schemes, m.intensity_props, m.use_mask_for_norm)
+            t2 = time.perf_counter()
+            x = torch.from_numpy(pre)
+            padded, _, _ = nnunet_inf.pad_to_patch(x, m.patch_size)
+            steps = nnunet_inf.compute_steps_for_sliding_window(padded.shape[2:], m.patch_size, 0.5)
+            n_tiles = len(steps[0]) * len(steps[1])
+            tile = padded[:, 0, :m.patch_size[0], :m.patch_size[1]][None]
+            t3 = time.perf_counter()
+            pred = nnunet_inf.maybe_mirror_and_predict(m.net(m.state_dicts[0]), tile, m.mirror_axes if self.mirror else None)
+            t4 = time.perf_counter()
+            logits = pred[0][:, None, :pre.shape[2], :pre.shape[3]]
+            if logits.shape[2:] != pre.shape[2:]:      # image taller than one tile: export a full-size logit map
+                logits = torch.nn.functional.pad(logits, (0, pre.shape[3] - logits.shape[3], 0, pre.shape[2] - logits.shape[2]))
+            seg = nnunet_inf.export_multilabel(logits.numpy(), props, "ideal")
+            t5 = time.perf_counter()
+        n_models = len(self.groups)
+        study = (t1 - t0) + n_models * ((t2 - t1) + n_tiles * (t4 - t3) + (t5 - t4))
+        return {"study_seconds": study, "projected": t1 - t0, "preprocessed": t2 - t1, "tile_predicted": t4 - t3, "exported": t5 - t4,
+                "n_tiles": n_tiles, "n_models": n_models, "mask_shape": list(seg.shape)}
+
+    def describe(self, shape) -> str:
+        return ("1 study {}x{}x{} int16: projection (full volume) + preprocess + 1 of T tiles x {} mirror passes of 1 of {} "
+                "group models + export, scaled to T tiles x {} models").format(shape[2], shape[1], shape[0], 4 if self.mirror else 1,
+                                                                               len(self.groups), len(self.groups))
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path.  The reference itself cannot run here
+    (SimpleITK / nnunetv2ml / weights are not installable offline), so this is the oracle port."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    shape = (96, 64, 160) if args.small else VOL_SHAPE
+    with tempfile.TemporaryDirectory() as tmp:
+        groups, patch = write_zoo(tmp, args.small, bool(args.mirror), only=("ribs",))
+        ref = CpuReference(tmp, groups, bool(args.mirror))
+        vol = synthetic_volume(20260000, shape)
+        times = []
+        for i in range(args.warmup + args.steps):
+            s = ref.sample(vol)
+            if i >= args.warmup:
+                times.append(s)
+    study = float(np.mean([t["study_seconds"] for t in times])) if times else float("nan")
+    v = 1.0 / study
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1000.0 * study, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": config_dict(args, shape, patch, 1),
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": ref.cores, "kind": "port", "sample": ref.describe(shape),
+                             "stage_seconds": {k: float(np.mean([t[k] for t in times])) for k in ("projected", "preprocessed", "tile_predicted", "exported")}},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def config_dict(args, shape, patch, studies_per_step):
+    return {"workload": "ts2d-v2 5-model pipeline, synthetic CT {}x{}x{} int16 1.5mm, CS-{} plan, 117 labels".format(shape[2], shape[1], shape[0], patch[0]),
+            "studies_per_step_per_gpu": studies_per_step, "tile_step_size": 0.5, "mirror_tta": bool(args.mirror), "models": 5,
+            "parallelism": "studies sharded over GPUs, no collective", "l2": "inputs larger than L2 (524 MB per study)",
+            "small": bool(args.small)}
+
+
+# ----------------------------------------------------------------------------------------------------------
+# GPU leg
+# ----------------------------------------------------------------------------------------------------------
+def dist_setup(args):
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    return world, rank, local
+
+
+def barrier(world):
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def max_over_ranks(x: float, world) -> float:
+    if world == 1:
+        return x
+    import torch.distributed as dist
+    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def sum_over_ranks(x: float, world) -> float:
+    if world == 1:
+        return x
+    import torch.distributed as dist
+    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return float(t.item())
+
+
+def run_b200(args):
+    from totalsegmentator2d_b200 import _lib as L
+    from totalsegmentator2d_b200.image import Image
+    from totalsegmentator2d_b200.tool import TS2D
+
+    world, rank, local = dist_setup(args)
+    peaks, peak_src = load_peaks()
+    shape = (96, 64, 160) if args.small else VOL_SHAPE
+    S = max(1, args.studies_per_step)
+    tmp = tempfile.TemporaryDirectory()
+    # every rank writes its own copy of the zoo (same seeds -> same weights), no shared-filesystem assumption
+    groups, patch = write_zoo(tmp.name, args.small, bool(args.mirror))
+    lib = L.load(check_device=True)
+
+    ts = TS2D(key="ts2d", models_root=tmp.name, param={"b200.precision": args.precision})
+    n_heads = ts.head_offsets()[-1]
+
+    # synthetic studies: S distinct volumes per rank, pinned on the host and resident in HBM
+    host_vols = []
+    for i in range(S):
+        v = torch.from_numpy(synthetic_volume(20260000 + rank * S + i, shape)).pin_memory()
+        host_vols.append(v)
+    dev_vols = [v.cuda(non_blocking=True) for v in host_vols]
+    H, W = shape[0], shape[2]
+    masks = [torch.zeros((H, W, n_heads), dtype=torch.uint8, device="cuda") for _ in range(S)]
+    presents = [torch.zeros(n_heads, dtype=torch.uint8, device="cuda") for _ in range(S)]
+    torch.cuda.synchronize()
+
+    def step_device():
+        for i in range(S):
+            ts.predict_volume_device(dev_vols[i], SPACING, None, mask=masks[i], present=presents[i])
+
+    def launches_now():
+        return int(lib.ts2d_launch_count())
+
+    # ---- value: device-resident ---------------------------------------------------------------------------
+    for _ in range(max(3, args.warmup)):
+        step_device()
+    barrier(world)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = launches_now()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step_device()
+    e1.record()
+    torch.cuda.synchronize()
+    ms_local = e0.elapsed_time(e1)
+    barrier(world)
+    launches = launches_now() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    ms_total = max_over_ranks(ms_local, world)
+    studies_total = S * args.steps * world
+    value = studies_total / (ms_total / 1000.0)
+
+    # ---- per-kernel evidence (separate pass right after the timed region, same process, same inputs) ---------
+    preds = [ts.models[m].predictor for m in ts.models]
+    for p in preds:
+        p.set_profiling(True)
+    ts.predict_volume_device(dev_vols[0], SPACING, None, mask=masks[0], present=presents[0])
+    torch.cuda.synchronize()
+    conv_ms = sum(p.last_conv_ms() for p in preds)
+    for p in preds:
+        p.set_profiling(False)
+    M = 4 if args.mirror else 1
+    tiles_per_model = 0
+    from totalsegmentator2d_b200.core.inference.predictor import sliding_window_layout
+    _, _, tiles = sliding_window_layout((H, W), patch, 0.5)
+    tiles_per_model = len(tiles)
+    conv_flops = sum(p.flops(tiles_per_model * M) for p in preds)
+    conv_tflops = conv_flops / (conv_ms * 1e-3) / 1e12 if conv_ms > 0 else 0.0
+    # projection kernel alone
+    from totalsegmentator2d_b200 import ops
+    pe0, pe1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    out = torch.empty((2, H, W), dtype=torch.float32, device="cuda")
+    reps = 10
+    pms = []
+    for r in range(reps):
+        v = dev_vols[r % S]
+        pe0.record()
+        ops.project(v, ["mean", "max"], reduce_dim=1, h_dim=0, out=out)
+        pe1.record()
+        torch.cuda.synchronize()
+        pms.append(pe0.elapsed_time(pe1))
+    proj_ms = float(np.median(pms))
+    proj_bytes = shape[0] * shape[1] * shape[2] * 2 + 2 * H * W * 4
+    proj_gbs = proj_bytes / (proj_ms * 1e-3) / 1e9
+
+    # ---- e2e: public API, host buffers ------------------------------------------------------------------------
+    e2e = None
+    if not args.skip_e2e:
+        imgs = [Image(host_vols[i].numpy(), SPACING, (0.0, 0.0, 0.0), np.eye(3).reshape(-1)) for i in range(S)]
+
+        def step_e2e():
+            nbytes_out = 0
+            for i in range(S):
+                res = ts.predict(imgs[i])
+                seg = res.get_segmentation()
+                nbytes_out += seg.array.nbytes
+            return nbytes_out
+
+        for _ in range(3):
+            step_e2e()
+        barrier(world)
+        t0 = time.perf_counter()
+        d2h = 0
+        for _ in range(args.steps):
+            d2h = step_e2e()
+        torch.cuda.synchronize()
+        t_local = time.perf_counter() - t0
+        barrier(world)
+        t_e2e = max_over_ranks(t_local, world)
+        e2e = {"value": studies_total / t_e2e, "unit": UNIT, "h2d_bytes_per_step": int(S * host_vols[0].numel() * 2),
+               "d2h_bytes_per_step": int(d2h + S * 2 * H * W * 4), "ms_per_step": 1000.0 * t_e2e / args.steps,
+               "api": "TS2D.predict(Image) + Result.get_segmentation()"}
+
+    # ---- cpu baseline (rank 0, N=1 only) ---------------------------------------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.skip_cpu:
+        ref = CpuReference(tmp.name, groups, bool(args.mirror))
+        s = ref.sample(host_vols[0].numpy())
+        cpu = {"value": 1.0 / s["study_seconds"], "unit": UNIT, "cores": ref.cores, "kind": "port", "sample": ref.describe(shape),
+               "stage_seconds": {k: s[k] for k in ("projected", "preprocessed", "tile_predicted", "exported")}}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+                "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": args.precision, "data": "synthetic", "config": config_dict(args, shape, patch, S),
+                "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+                "roofline": {"bound": "tensor", "kernel": "conv_tc_kernel (tcgen05 implicit-GEMM conv, all conv/transposed-conv launches of one study)",
+                             "achieved": conv_tflops, "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
+                             "frac": conv_tflops / peaks["bf16_tflops_sustained"], "traffic": None, "peak_source": peak_src + " (sustained)",
+                             "conv_ms_per_study": conv_ms, "conv_flops_per_study": conv_flops},
+                "roofline_hbm": {"bound": "hbm", "kernel": "project_strided_i16_kernel", "achieved": proj_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                                 "frac": proj_gbs / peaks["hbm_gbs"], "traffic": None, "peak_source": peak_src, "ms": proj_ms, "bytes": proj_bytes},
+                "cpu_baseline": cpu}
+        print(json.dumps(line))
+    ts.close()
+    tmp.cleanup()
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

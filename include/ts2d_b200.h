@@ -92,7 +92,7 @@ int ts2d_resample2d(const float *in_dev, int C, int h, int w, float *out_dev, in
  * axes_combinations: m=0 none, then (H), (W), (H,W) for mirror_axes (0,1).
  * mirror_mask: bit0 = axis H allowed, bit1 = axis W allowed. M = 1,2 or 4 accordingly.
  */
-int ts2d_extract_tiles(const float *img_dev, int C, int h, int w, int pad_top, int pad_left,
+int ts2d_extract_tiles(const float *img_dev, int C, int h, int w, int pad_top, int pad_left, /* T <= 1024 */
                        int Ph, int Pw, const int *tile_yx_host, int T, int mirror_mask,
                        int precision, void *out_dev, ts2d_stream stream);
 

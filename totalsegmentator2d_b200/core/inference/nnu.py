@@ -172,14 +172,14 @@ class NNUDeviceModel(NNUModel):
         return seg
 
     def predict_device(self, img_dev: torch.Tensor, spacing_xy, mask: Optional[torch.Tensor] = None, ch_off: int = 0,
-                       present: Optional[torch.Tensor] = None, cache: Optional[dict] = None) -> torch.Tensor:
+                       present: Optional[torch.Tensor] = None, cache: Optional[dict] = None, cache_key=()) -> torch.Tensor:
         """(C, H, W) float32 CUDA image -> uint8 mask [H][W][ch_total] on the device (this model's channel window).
         Stage order = reference prediction_worker.py:194-221: preprocess -> predict -> export."""
         p = self.predictor
         C, H, W = img_dev.shape
         if mask is None:
             mask = torch.zeros((H, W, p.num_heads), dtype=torch.uint8, device=img_dev.device)
-        key = self.preprocess_key()
+        key = self.preprocess_key() + tuple(cache_key)
         entry = cache.get(key) if cache is not None else None
         if entry is None:
             data, props = B200Preprocessor().run_case_device(img_dev, spacing_xy, p.plans_manager, p.configuration_manager, self.dataset_json)

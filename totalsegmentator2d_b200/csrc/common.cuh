@@ -70,6 +70,14 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
+// sliding-window tile origins (y, x) in padded coordinates, passed by value in kernel-parameter space
+constexpr int kMaxTiles = 1024;
+template <int CAP> struct TileListT { int T; int yx[CAP][2]; };
+template <int CAP> static inline void fill_tile_list(TileListT<CAP> &tl, const int *yx_host, int T) {
+    tl.T = T;
+    for (int t = 0; t < T; ++t) { tl.yx[t][0] = yx_host[2 * t]; tl.yx[t][1] = yx_host[2 * t + 1]; }
+}
+
 static inline size_t prec_size(int precision) { return precision == TS2D_PREC_F32 ? 4 : 2; }
 
 }  // namespace ts2d

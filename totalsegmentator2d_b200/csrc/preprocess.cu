@@ -218,10 +218,11 @@ __global__ void __launch_bounds__(256) threshold_logits_kernel(const float *lg, 
 }
 
 // ---------------- sliding-window tile extraction: pad + slice + mirror + cast + NCHW->NHWC ---------------------------
-struct TileList { int T; int yx[64][2]; };
-template <typename T>
+// tile origins travel in kernel-parameter space (sm_70+ accepts 32 KB of parameters): 64 tiles cover every
+// production layout (512x512x2000 study = 7 tiles), the 1024-tile variant serves small-patch plans
+template <typename T, int CAP>
 __global__ void __launch_bounds__(256) extract_tiles_kernel(const float *img, int C, int h, int w, int pad_top, int pad_left, int Ph, int Pw,
-                                                            TileList tl, int M, int mirror_mask, T *out) {
+                                                            const __grid_constant__ TileListT<CAP> tl, int M, int mirror_mask, T *out) {
     const int img_idx = blockIdx.y;                 // t*M + m
     const int t = img_idx / M, m = img_idx % M;
     // upstream axes_combinations order for allowed axes (H, W): (), (H), (W), (H, W); with one allowed axis: (), (that axis)
@@ -339,18 +340,22 @@ extern "C" int ts2d_threshold_logits(const float *logits_dev, int heads, int h, 
 
 extern "C" int ts2d_extract_tiles(const float *img_dev, int C, int h, int w, int pad_top, int pad_left, int Ph, int Pw, const int *tile_yx_host,
                                   int T, int mirror_mask, int precision, void *out_dev, ts2d_stream stream) {
-    TS2D_REQUIRE(img_dev && out_dev && tile_yx_host && C > 0 && T > 0 && T <= 64, "ts2d_extract_tiles: bad arguments (T must be 1..64)");
+    TS2D_REQUIRE(img_dev && out_dev && tile_yx_host && C > 0 && T > 0 && T <= kMaxTiles, "ts2d_extract_tiles: bad arguments (T must be 1..%d)", kMaxTiles);
     TS2D_REQUIRE(mirror_mask >= 0 && mirror_mask <= 3, "ts2d_extract_tiles: bad mirror mask");
-    TileList tl;
-    tl.T = T;
-    for (int t = 0; t < T; ++t) { tl.yx[t][0] = tile_yx_host[2 * t]; tl.yx[t][1] = tile_yx_host[2 * t + 1]; }
+    TS2D_REQUIRE(precision >= 0 && precision <= 2, "ts2d_extract_tiles: bad precision %d", precision);
     const int M = mirror_mask == 3 ? 4 : (mirror_mask ? 2 : 1);
     dim3 grid(grid_for((long long)Ph * Pw * C, 256, kNumSMs * 4), T * M);
     cudaStream_t st = (cudaStream_t)stream;
-    if (precision == TS2D_PREC_F32) extract_tiles_kernel<float><<<grid, 256, 0, st>>>(img_dev, C, h, w, pad_top, pad_left, Ph, Pw, tl, M, mirror_mask, (float *)out_dev);
-    else if (precision == TS2D_PREC_BF16) extract_tiles_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(img_dev, C, h, w, pad_top, pad_left, Ph, Pw, tl, M, mirror_mask, (__nv_bfloat16 *)out_dev);
-    else if (precision == TS2D_PREC_F16) extract_tiles_kernel<__half><<<grid, 256, 0, st>>>(img_dev, C, h, w, pad_top, pad_left, Ph, Pw, tl, M, mirror_mask, (__half *)out_dev);
-    else { set_error("ts2d_extract_tiles: bad precision %d", precision); return TS2D_ERR_ARG; }
+#define TS2D_EXTRACT(CAP)                                                                                                                      \
+    do {                                                                                                                                       \
+        TileListT<CAP> tl;                                                                                                                     \
+        fill_tile_list(tl, tile_yx_host, T);                                                                                                   \
+        if (precision == TS2D_PREC_F32) extract_tiles_kernel<float, CAP><<<grid, 256, 0, st>>>(img_dev, C, h, w, pad_top, pad_left, Ph, Pw, tl, M, mirror_mask, (float *)out_dev); \
+        else if (precision == TS2D_PREC_BF16) extract_tiles_kernel<__nv_bfloat16, CAP><<<grid, 256, 0, st>>>(img_dev, C, h, w, pad_top, pad_left, Ph, Pw, tl, M, mirror_mask, (__nv_bfloat16 *)out_dev); \
+        else extract_tiles_kernel<__half, CAP><<<grid, 256, 0, st>>>(img_dev, C, h, w, pad_top, pad_left, Ph, Pw, tl, M, mirror_mask, (__half *)out_dev); \
+    } while (0)
+    if (T <= 64) TS2D_EXTRACT(64); else TS2D_EXTRACT(kMaxTiles);
+#undef TS2D_EXTRACT
     TS2D_LAUNCH_CHECK();
     return TS2D_OK;
 }

@@ -697,27 +697,33 @@ extern "C" int ts2d_unet_tile_logits(ts2d_unet *u, int batch, float *logits_dev,
     return TS2D_OK;
 }
 
-template <typename T>
-static int launch_blend(const BlendParams &p, int F, cudaStream_t st) {
+template <typename T, int CAP>
+static int launch_blend(const BlendParams &p, const int *tile_yx_host, int F, cudaStream_t st) {
     const long long npix = (long long)p.h * p.w;
     const int grid = ceil_div(npix, 128);
     const size_t smem = (size_t)(p.heads * F + p.heads) * sizeof(float);
+    TileListT<CAP> tl;
+    fill_tile_list(tl, tile_yx_host, p.T);
     switch (F) {
-        case 8: blend_head_kernel<T, 8><<<grid, 128, smem, st>>>(p); break;
-        case 16: blend_head_kernel<T, 16><<<grid, 128, smem, st>>>(p); break;
-        case 32: blend_head_kernel<T, 32><<<grid, 128, smem, st>>>(p); break;
-        case 64: blend_head_kernel<T, 64><<<grid, 128, smem, st>>>(p); break;
+        case 8: blend_head_kernel<T, 8, CAP><<<grid, 128, smem, st>>>(p, tl); break;
+        case 16: blend_head_kernel<T, 16, CAP><<<grid, 128, smem, st>>>(p, tl); break;
+        case 32: blend_head_kernel<T, 32, CAP><<<grid, 128, smem, st>>>(p, tl); break;
+        case 64: blend_head_kernel<T, 64, CAP><<<grid, 128, smem, st>>>(p, tl); break;
         default: set_error("ts2d_unet_blend_head: features_per_stage[0] must be 8, 16, 32 or 64 (got %d)", F); return TS2D_ERR_UNSUPPORTED;
     }
     TS2D_LAUNCH_CHECK();
     return TS2D_OK;
+}
+template <typename T>
+static int launch_blend_any(const BlendParams &p, const int *tile_yx_host, int F, cudaStream_t st) {
+    return p.T <= 64 ? launch_blend<T, 64>(p, tile_yx_host, F, st) : launch_blend<T, kMaxTiles>(p, tile_yx_host, F, st);
 }
 
 extern "C" int ts2d_unet_blend_head(ts2d_unet *u, const int *tile_yx_host, int T, int M, int mirror_mask, int pad_top, int pad_left, int h, int w,
                                     const float *gaussian_dev, float *logits_dev, uint8_t *mask_dev, int H0, int W0, int h0, int w0, int ch_off,
                                     int ch_total, uint8_t *present_dev, ts2d_stream stream) {
     TS2D_REQUIRE(u && tile_yx_host && gaussian_dev, "ts2d_unet_blend_head: null pointer");
-    TS2D_REQUIRE(T >= 1 && T <= 64, "ts2d_unet_blend_head: T must be 1..64");
+    TS2D_REQUIRE(T >= 1 && T <= kMaxTiles, "ts2d_unet_blend_head: T must be 1..%d", kMaxTiles);
     TS2D_REQUIRE(M == (mirror_mask == 3 ? 4 : (mirror_mask ? 2 : 1)), "ts2d_unet_blend_head: M does not match the mirror mask");
     TS2D_REQUIRE(logits_dev || mask_dev, "ts2d_unet_blend_head: no output requested");
     if (!u->finalized || T * M > u->last_batch) { set_error("ts2d_unet_blend_head: the last forward ran %d images, %d needed", u->last_batch, T * M); return TS2D_ERR_STATE; }
@@ -727,16 +733,15 @@ extern "C" int ts2d_unet_blend_head(ts2d_unet *u, const int *tile_yx_host, int T
     BlendParams p;
     memset(&p, 0, sizeof(p));
     p.feat = u->features; p.T = T; p.M = M; p.mirror_mask = mirror_mask; p.Ph = u->plan.patch_h; p.Pw = u->plan.patch_w;
-    for (int t = 0; t < T; ++t) { p.yx[t][0] = tile_yx_host[2 * t]; p.yx[t][1] = tile_yx_host[2 * t + 1]; }
     p.pad_top = pad_top; p.pad_left = pad_left; p.h = h; p.w = w;
     p.gauss = gaussian_dev; p.head_w = u->head_w.dev; p.head_b = u->head_b.dev; p.heads = u->plan.num_heads;
     p.logits = logits_dev; p.mask = mask_dev; p.W0 = W0; p.h0 = h0; p.w0 = w0; p.ch_off = ch_off; p.ch_total = ch_total;
     p.present = present_dev;
     cudaStream_t st = (cudaStream_t)stream;
     int rc;
-    if (u->plan.precision == TS2D_PREC_F32) rc = launch_blend<float>(p, u->C[0], st);
-    else if (u->plan.precision == TS2D_PREC_BF16) rc = launch_blend<__nv_bfloat16>(p, u->C[0], st);
-    else rc = launch_blend<__half>(p, u->C[0], st);
+    if (u->plan.precision == TS2D_PREC_F32) rc = launch_blend_any<float>(p, tile_yx_host, u->C[0], st);
+    else if (u->plan.precision == TS2D_PREC_BF16) rc = launch_blend_any<__nv_bfloat16>(p, tile_yx_host, u->C[0], st);
+    else rc = launch_blend_any<__half>(p, tile_yx_host, u->C[0], st);
     if (rc) return rc;
     u->launches++;
     return TS2D_OK;

@@ -148,7 +148,6 @@ __global__ void __launch_bounds__(256) norm_act_kernel(const T *raw, const doubl
 // ------------------------------------------------------------------------------------------------------
 struct BlendParams {
     const void *feat; int T, M, mirror_mask; int Ph, Pw;
-    int yx[64][2];
     int pad_top, pad_left, h, w;
     const float *gauss;        // [Ph][Pw]
     const float *head_w;       // [heads][F]
@@ -160,8 +159,8 @@ struct BlendParams {
     uint8_t *present;          // [ch_total] or null
 };
 
-template <typename T, int F>
-__global__ void __launch_bounds__(128) blend_head_kernel(const BlendParams p) {
+template <typename T, int F, int CAP>
+__global__ void __launch_bounds__(128) blend_head_kernel(const BlendParams p, const __grid_constant__ TileListT<CAP> tl) {
     extern __shared__ float s_head[];            // head_w [heads][F] then head_b[heads]
     for (int i = threadIdx.x; i < p.heads * F; i += blockDim.x) s_head[i] = p.head_w[i];
     for (int i = threadIdx.x; i < p.heads; i += blockDim.x) s_head[p.heads * F + i] = p.head_b ? p.head_b[i] : 0.f;
@@ -177,7 +176,7 @@ __global__ void __launch_bounds__(128) blend_head_kernel(const BlendParams p) {
     const T *feat = reinterpret_cast<const T *>(p.feat);
     const float inv_m = 1.0f / (float)p.M;
     for (int t = 0; t < p.T; ++t) {
-        const int ly = yp - p.yx[t][0], lx = xp - p.yx[t][1];
+        const int ly = yp - tl.yx[t][0], lx = xp - tl.yx[t][1];
         if (ly < 0 || ly >= p.Ph || lx < 0 || lx >= p.Pw) continue;
         const float g = p.gauss[ly * p.Pw + lx];
         wsum += g;

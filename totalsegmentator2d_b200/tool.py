@@ -104,6 +104,75 @@ class TS2D:
             pass
 
     # ------------------------------------------------------------------------------------------------
+    # device-level core (what ``predict`` runs between the H2D copy of the input and the D2H copy of the mask)
+    def _channel_defs(self):
+        defs = dict()
+        for id, model in self.models.items():
+            ch = model.channels
+            if ch is None:
+                raise RuntimeError(f"Model {id} does not have a channel definition, cannot project the input image.")
+            defs[id] = sorted(ch.items(), key=lambda x: x[0])          # reference tool.py:145-148
+        return defs
+
+    def head_offsets(self):
+        heads = [self.models[id].predictor.num_heads for id in self.models]
+        return [int(v) for v in np.concatenate([[0], np.cumsum(heads)])]
+
+    def predict_image_device(self, imgs_dev: Dict[str, torch.Tensor], spacing_xy, mask: Optional[torch.Tensor] = None,
+                             present: Optional[torch.Tensor] = None) -> dict:
+        """imgs_dev: {model id: float32 CUDA (C, H, W)} -> {'mask': uint8 [H][W][sum heads] (model-id order, label order),
+        'present': uint8 [sum heads], 'offsets': channel window of each model}.  Everything stays in HBM.
+        Models whose preprocessing agrees share the preprocessed image and its tiles (the reference preprocesses
+        per model inside each worker, prediction_worker.py:194-199)."""
+        ids = list(self.models.keys())
+        offs = self.head_offsets()
+        first = imgs_dev[ids[0]]
+        H, W = int(first.shape[1]), int(first.shape[2])
+        if mask is None:
+            mask = torch.zeros((H, W, offs[-1]), dtype=torch.uint8, device=first.device)
+        else:
+            mask.zero_()
+        if present is None:
+            present = torch.zeros(offs[-1], dtype=torch.uint8, device=first.device)
+        else:
+            present.zero_()
+        cache = dict()
+        for k, id in enumerate(ids):
+            try:
+                key = (imgs_dev[id].data_ptr(),)
+                self.models[id].predict_device(imgs_dev[id], spacing_xy, mask=mask, ch_off=offs[k], present=present, cache=cache, cache_key=key)
+            except L.TS2DError as ex:
+                raise RuntimeError(f"Prediction failed for: {id} ({ex})") from ex
+        return {"mask": mask, "present": present, "offsets": offs}
+
+    def predict_volume_device(self, vol_dev: torch.Tensor, spacing_xyz, direction=None, mask: Optional[torch.Tensor] = None,
+                              present: Optional[torch.Tensor] = None) -> dict:
+        """vol_dev: CUDA tensor [z][y][x] (sitk.GetArrayFromImage order) -> projections + merged mask, all in HBM.
+        reorient_image('RAI') (reference tool.py:154) is folded into the projection kernel's addressing; every channel
+        any model asks for comes out of one pass over the volume (reference: one ITK filter per channel, tool.py:156-159)."""
+        chan_defs = self._channel_defs()
+        names: List[str] = []
+        for id in self.models:
+            for _, n in chan_defs[id]:
+                if n not in names:
+                    names.append(n)
+        d = np.eye(3) if direction is None else np.asarray(direction, dtype=np.float64).reshape(3, 3)
+        perm, flip = orientation_remap(d, "RAI")
+        ax = axis_name_to_index("coronal")
+        out = ops.project(vol_dev, names, reduce_dim=2 - perm[ax], h_dim=2 - perm[2], flip_h=flip[2], flip_w=flip[0])
+        imgs = dict()
+        stacked = dict()
+        for id in self.models:
+            idx = tuple(names.index(n) for _, n in chan_defs[id])
+            if idx not in stacked:
+                stacked[idx] = out if idx == tuple(range(len(names))) else torch.stack([out[i] for i in idx], dim=0)
+            imgs[id] = stacked[idx]
+        sp = [float(spacing_xyz[perm[k]]) for k in range(3)]
+        res = self.predict_image_device(imgs, (sp[0], sp[2]), mask=mask, present=present)
+        res["projections"], res["channel_names"] = out, names
+        return res
+
+    # ------------------------------------------------------------------------------------------------
     def predict(self, input, collapse: bool = False, merge: bool = True):
         """
         Predict the segmentation for the given input image.
@@ -120,70 +189,44 @@ class TS2D:
 
         ids = list(self.models.keys())
         is3d = get_actual_dimension(input) > 2
-        chan_defs = dict()
-        for id in ids:
-            ch = self.models[id].channels
-            if ch is None:
-                raise RuntimeError(f"Model {id} does not have a channel definition, cannot project the input image.")
-            chan_defs[id] = sorted(ch.items(), key=lambda x: x[0])
+        chan_defs = self._channel_defs()
 
         result = dict()
         projections: Dict[str, Image] = dict()
-        proj_dev: Dict[str, torch.Tensor] = dict()
         if is3d:
-            # one pass: reorient (folded into addressing) + every projection any model asks for
-            names = []
-            for id in ids:
-                for _, n in chan_defs[id]:
-                    if n not in names:
-                        names.append(n)
+            vol = _to_device(input.array)
             perm, flip = orientation_remap(input.direction_matrix(), "RAI")
             size, sp, org, nd = _reoriented_geometry(input, perm, flip)
-            vol = _to_device(input.array)
             ax = axis_name_to_index("coronal")
-            out = ops.project(vol, names, reduce_dim=2 - perm[ax], h_dim=2 - perm[2], flip_h=flip[2], flip_w=flip[0])
+            dev = self.predict_volume_device(vol, input.GetSpacing(), input.direction_matrix())
             del vol
-            host = out.cpu().numpy()
-            for i, n in enumerate(names):
+            host = dev["projections"].cpu().numpy()
+            for i, n in enumerate(dev["channel_names"]):
                 projections[n] = _projected_image(host[i], size, sp, org, nd, ax)
-                proj_dev[n] = out[i]
-            spacing_xy = (sp[0], sp[2])
-            H, W = int(out.shape[1]), int(out.shape[2])
-            geo3d = projections[names[0]]
         else:
             base2d = input if input.GetDimension() < 3 else reduce_dimensions(input)
             chs = split_channels(input)
             projections.update((f"ch{i}", ch) for i, ch in enumerate(chs))
+            input_nch = input.GetNumberOfComponentsPerPixel()
+            for id in ids:
+                if len(chan_defs[id]) != input_nch:
+                    raise RuntimeError(f"The number of channels in the input image does not match the models channel definition ({len(chan_defs[id])} vs {input_nch}).")
             arr = np.asarray(base2d.array, dtype=np.float32)
             chw = np.moveaxis(arr, -1, 0) if base2d.is_vector else arr[None]
             img_dev_2d = torch.from_numpy(np.ascontiguousarray(chw)).cuda()
-            spacing_xy = base2d.GetSpacing()
-            H, W = int(chw.shape[1]), int(chw.shape[2])
+            dev = self.predict_image_device({id: img_dev_2d for id in ids}, base2d.GetSpacing())
+        mask, present, offs = dev["mask"], dev["present"], dev["offsets"]
 
-        heads = [self.models[id].predictor.num_heads for id in ids]
-        offs = np.concatenate([[0], np.cumsum(heads)]).astype(int)
-        total = int(offs[-1])
-        mask = torch.zeros((H, W, total), dtype=torch.uint8, device="cuda")
-        present = torch.zeros(total, dtype=torch.uint8, device="cuda")
-        cache = dict()
         model_inputs = dict()
         for k, id in enumerate(ids):
             model = self.models[id]
             res = {"id": id, "revision": model.revision}
             res["model"], res["group"] = decompose_model_key(id)
             if is3d:
-                img_dev = torch.stack([proj_dev[n] for _, n in chan_defs[id]], dim=0)
                 ch_list = [projections[n] for _, n in chan_defs[id]]
                 minput = compose(ch_list) if len(ch_list) > 1 else ch_list[0]
             else:
-                model_nch, input_nch = len(chan_defs[id]), input.GetNumberOfComponentsPerPixel()
-                if model_nch != input_nch:
-                    raise RuntimeError(f"The number of channels in the input image does not match the models channel definition ({model_nch} vs {input_nch}).")
-                img_dev, minput = img_dev_2d, input
-            try:
-                model.predict_device(img_dev, spacing_xy, mask=mask, ch_off=int(offs[k]), present=present, cache=cache)
-            except L.TS2DError as ex:
-                raise RuntimeError(f"Prediction failed for: {id} ({ex})") from ex
+                minput = input
             native_2d = minput.GetDimension() < 3
             input2d = minput if native_2d else reduce_dimensions(minput)
             model_inputs[id] = (minput, input2d, native_2d)
