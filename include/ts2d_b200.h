@@ -170,6 +170,11 @@ double ts2d_unet_flops(const ts2d_unet *u, int batch);
 /* device time (ms) the conv kernels of the last forward took; needs ts2d_unet_set_profiling(u, 1) */
 int ts2d_unet_set_profiling(ts2d_unet *u, int enable);
 double ts2d_unet_last_conv_ms(ts2d_unet *u);
+/* per-launch record of the last profiled forward: kind 0 = conv, 1 = transposed conv, 2 = InstanceNorm-apply;
+ * flops / bytes are the ALGORITHMIC figures of that launch (MAC = 2; bytes = activations read once + written once) */
+int ts2d_unet_profile_count(const ts2d_unet *u);
+int ts2d_unet_profile_entry(ts2d_unet *u, int i, char *name_out, int name_cap, int *kind, double *ms,
+                            double *flops, double *bytes);
 int ts2d_unet_destroy(ts2d_unet *u);
 
 /* global launch counter of the non-engine kernels (projection, preprocessing, tiling) */

@@ -110,4 +110,4 @@ def test_errors_are_loud():
     with pytest.raises(L.TS2DError):
         p.predict_logits_from_preprocessed_data(torch.zeros(2, 16, 16))
     with pytest.raises(L.TS2DError):
-        _make([8, 16], (18, 18))                      # patch not divisible by the strides
+        _make([8, 16], (17, 17))                      # patch not divisible by the strides

@@ -205,6 +205,17 @@ class B200nnUNetPredictor:
     def last_conv_ms(self) -> float:
         return sum(float(self._lib.ts2d_unet_last_conv_ms(h)) for h in self._handles)
 
+    def layer_profile(self, fold: int = 0):
+        """[(name, kind, ms, algorithmic flops, algorithmic bytes)] of the last profiled forward"""
+        h = self._handles[fold]
+        out = []
+        for i in range(int(self._lib.ts2d_unet_profile_count(h))):
+            buf = C.create_string_buffer(64)
+            kind, ms, fl, by = C.c_int(), C.c_double(), C.c_double(), C.c_double()
+            L.check(self._lib.ts2d_unet_profile_entry(h, i, buf, 64, C.byref(kind), C.byref(ms), C.byref(fl), C.byref(by)))
+            out.append((buf.value.decode(), int(kind.value), float(ms.value), float(fl.value), float(by.value)))
+        return out
+
     def _ensure_batch(self, n: int):
         if n > self.max_batch:
             for h in self._handles:

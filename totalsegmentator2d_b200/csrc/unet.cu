@@ -17,6 +17,7 @@
 #include <vector>
 
 #include "conv_tc.cuh"
+#include "conv_halo.cuh"
 #include "unet_kernels.cuh"
 
 namespace ts2d {
@@ -57,6 +58,9 @@ struct ConvLayer {
     int bn = 0, kc = 0, enc_n = 0;
     CUtensorMap tmA, tmB;
     bool first = false;         // reads the caller's tiles: tmA encoded per forward
+    bool halo = false;          // conv_halo_kernel (3x3 stride 1, halo tile + resident weights)
+    int halo_bn = 0, halo_stages = 0;
+    bool halo_maps = false;
 };
 
 struct UpLayer {
@@ -102,6 +106,8 @@ struct ts2d_unet {
     bool profiling = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
     int prof_used = 0;
+    struct ProfEntry { std::string name; int kind; double flops, bytes; };   // kind 0 conv, 1 up, 2 norm
+    std::vector<ProfEntry> prof_entries;
 };
 
 namespace ts2d {
@@ -194,6 +200,56 @@ static int launch_tc(int bn, int kc, const CUtensorMap &tmA, const CUtensorMap &
 #undef TS2D_TC_CASE
     set_error("no tensor-core conv instantiation for BN=%d KC=%d", bn, kc);
     return TS2D_ERR_UNSUPPORTED;
+}
+
+constexpr int kHaloSmemBudget = 225 * 1024;
+static int halo_smem_bytes(int cin, int bn, int kc, int stages) {
+    const int w = ((9 * cin * bn * 2) + 1023) & ~1023;
+    const int st = kc == 64 ? halo_stage_bytes<64>() : halo_stage_bytes<32>();
+    return 1024 /*align*/ + w + stages * st + 512 /*barriers*/ + bn * 4 + 64;
+}
+template <int BN, int KC, typename DT, bool FUSE>
+static int launch_halo_inst(const CUtensorMap &tmA, const CUtensorMap &tmB, const ConvHaloParams &p, int smem, cudaStream_t st) {
+    static int attr_smem = 0;
+    if (smem > attr_smem) {
+        TS2D_CHECK_CUDA(cudaFuncSetAttribute(conv_halo_kernel<BN, KC, DT, FUSE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHaloSmemBudget));
+        attr_smem = kHaloSmemBudget;
+    }
+    const int n_tiles_n = p.Cout / BN;
+    const int total = p.tiles_x * p.tiles_y * p.N;
+    const int gx = std::max(1, std::min(total, kNumSMs / n_tiles_n));
+    conv_halo_kernel<BN, KC, DT, FUSE><<<dim3(gx, n_tiles_n), FUSE ? 320 : 192, smem, st>>>(tmA, tmB, p);
+    TS2D_LAUNCH_CHECK();
+    return TS2D_OK;
+}
+template <typename DT>
+static int launch_halo(int bn, int kc, bool fuse, const CUtensorMap &tmA, const CUtensorMap &tmB, const ConvHaloParams &p, int smem, cudaStream_t st) {
+#define TS2D_HALO_CASE(B, K)                                                              \
+    if (bn == B && kc == K) return fuse ? launch_halo_inst<B, K, DT, true>(tmA, tmB, p, smem, st) \
+                                        : launch_halo_inst<B, K, DT, false>(tmA, tmB, p, smem, st);
+    TS2D_HALO_CASE(32, 32) TS2D_HALO_CASE(64, 32) TS2D_HALO_CASE(32, 64) TS2D_HALO_CASE(64, 64)
+#undef TS2D_HALO_CASE
+    set_error("no halo conv instantiation for BN=%d KC=%d", bn, kc);
+    return TS2D_ERR_UNSUPPORTED;
+}
+
+// picks the output-channel block and ring depth of the halo kernel, or returns false when the layer should use conv_tc_kernel
+static bool halo_config(const ConvLayer &c, int &bn, int &stages) {
+    static const int enable = getenv("TS2D_CONV_HALO") ? atoi(getenv("TS2D_CONV_HALO")) : 1;
+    static const int max_nt = getenv("TS2D_HALO_MAX_NT") ? atoi(getenv("TS2D_HALO_MAX_NT")) : 2;
+    if (!enable || !c.tc || c.kh != 3 || c.kw != 3 || c.sh != 1 || c.sw != 1) return false;
+    if (c.Hout < 16 || c.Wout < 8) return false;
+    const double covered = (double)ceil_div(c.Wout, 8) * 8 * ceil_div(c.Hout, 16) * 16;
+    if (covered > 1.3 * c.Wout * c.Hout) return false;
+    for (int b : {64, 32}) {
+        if (c.cout % b || c.cout / b > max_nt) continue;
+        int st = 6;
+        while (st >= 2 && halo_smem_bytes(c.cin, b, c.kc, st) > kHaloSmemBudget) --st;
+        if (st < 2) continue;
+        bn = b; stages = st;
+        return true;
+    }
+    return false;
 }
 
 template <typename T> static int launch_direct(const DirectConvParams &p, int N, cudaStream_t st) {
@@ -486,6 +542,8 @@ extern "C" int ts2d_unet_finalize(ts2d_unet *u) {
         if ((rc = upload(c.b)) || (rc = upload(c.gamma)) || (rc = upload(c.beta))) return rc;
         if (c.tc) c.kc = (c.cin % 64 == 0) ? 64 : 32;
         c.enc_n = 0;
+        c.halo = halo_config(c, c.halo_bn, c.halo_stages);
+        c.halo_maps = false;
     }
     for (auto &up : u->ups) {
         up.tc = tc_eligible(pl, up.cin, up.cout, 1, 1, 1, 1, up.Hin, up.Win, up.cin);
@@ -514,21 +572,51 @@ extern "C" double ts2d_unet_flops(const ts2d_unet *u, int batch) {
 
 namespace ts2d {
 
+static int prof_begin(ts2d_unet *u, cudaStream_t st) {
+    if (!u->profiling) return TS2D_OK;
+    if (u->prof_used >= (int)u->prof_events.size()) {
+        cudaEvent_t a, b;
+        TS2D_CHECK_CUDA(cudaEventCreate(&a));
+        TS2D_CHECK_CUDA(cudaEventCreate(&b));
+        u->prof_events.push_back({a, b});
+    }
+    TS2D_CHECK_CUDA(cudaEventRecord(u->prof_events[u->prof_used].first, st));
+    return TS2D_OK;
+}
+static int prof_end(ts2d_unet *u, const std::string &name, int kind, double flops, double bytes, cudaStream_t st) {
+    if (!u->profiling) return TS2D_OK;
+    TS2D_CHECK_CUDA(cudaEventRecord(u->prof_events[u->prof_used].second, st));
+    if ((int)u->prof_entries.size() <= u->prof_used) u->prof_entries.resize(u->prof_used + 1);
+    u->prof_entries[u->prof_used] = {name, kind, flops, bytes};
+    u->prof_used++;
+    return TS2D_OK;
+}
+
 static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
     const ts2d_unet_plan &pl = u->plan;
     const size_t es = u->es;
     const bool is_bf16 = pl.precision == TS2D_PREC_BF16;
     int rc;
-    if (u->profiling) {
-        if (u->prof_used >= (int)u->prof_events.size()) {
-            cudaEvent_t a, b;
-            TS2D_CHECK_CUDA(cudaEventCreate(&a));
-            TS2D_CHECK_CUDA(cudaEventCreate(&b));
-            u->prof_events.push_back({a, b});
+    if ((rc = prof_begin(u, st))) return rc;
+    if (c.halo) {
+        ConvHaloParams p;
+        memset(&p, 0, sizeof(p));
+        p.N = N; p.H = c.Hout; p.W = c.Wout; p.Cout = c.cout; p.n_base = 0;
+        p.cin_chunks = c.cin / c.kc;
+        p.tiles_x = ceil_div(c.Wout, 8); p.tiles_y = ceil_div(c.Hout, 16);
+        p.n_stages = c.halo_stages;
+        p.out_ps = c.cout; p.out = u->raw; p.bias = c.b.dev; p.stats = c.stats;
+        p.Cin = c.cin;
+        if (c.first || !c.halo_maps) {
+            if ((rc = encode_act_map(&c.tmA, c.in, c.in_ps, c.cin, c.Hin, c.Win, pl.max_batch, false, c.kc, kHaloW, kHaloH, 1, es, is_bf16))) return rc;
+            if ((rc = encode_w_map(&c.tmB, c.w_tc, c.cin, c.cout, 9, c.kc, c.halo_bn, es, is_bf16))) return rc;
+            c.halo_maps = true;
         }
-        TS2D_CHECK_CUDA(cudaEventRecord(u->prof_events[u->prof_used].first, st));
-    }
-    if (c.tc) {
+        const int smem = halo_smem_bytes(c.cin, c.halo_bn, c.kc, c.halo_stages);
+        rc = is_bf16 ? launch_halo<__nv_bfloat16>(c.halo_bn, c.kc, false, c.tmA, c.tmB, p, smem, st)
+                     : launch_halo<__half>(c.halo_bn, c.kc, false, c.tmA, c.tmB, p, smem, st);
+        if (rc) return rc;
+    } else if (c.tc) {
         ConvTcParams p;
         const bool s2 = c.sh == 2;
         int tw, th, tn;
@@ -560,14 +648,17 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
         if ((rc = launch_direct_any(pl.precision, p, N, st))) return rc;
     }
     u->launches++;
-    if (u->profiling) {
-        TS2D_CHECK_CUDA(cudaEventRecord(u->prof_events[u->prof_used].second, st));
-        u->prof_used++;
+    {
+        const double px = (double)N * c.Hout * c.Wout;
+        if ((rc = prof_end(u, c.name, 0, 2.0 * px * c.kh * c.kw * c.cin * c.cout,
+                           ((double)N * c.Hin * c.Win * c.cin + px * c.cout) * es, st))) return rc;
     }
+    if ((rc = prof_begin(u, st))) return rc;
     rc = launch_norm_any(pl.precision, u->raw, c.stats, c.gamma.dev, c.beta.dev, c.norm_out, c.out_ps, c.Hout * c.Wout, c.cout, pl.eps,
                          pl.negative_slope, N, st);
     if (rc) return rc;
     u->launches++;
+    if ((rc = prof_end(u, c.name + ".norm", 2, 0.0, 2.0 * N * c.Hout * c.Wout * c.cout * es, st))) return rc;
     return TS2D_OK;
 }
 
@@ -576,15 +667,7 @@ static int run_up(ts2d_unet *u, UpLayer &up, int N, cudaStream_t st) {
     const size_t es = u->es;
     const bool is_bf16 = pl.precision == TS2D_PREC_BF16;
     int rc;
-    if (u->profiling) {
-        if (u->prof_used >= (int)u->prof_events.size()) {
-            cudaEvent_t a, b;
-            TS2D_CHECK_CUDA(cudaEventCreate(&a));
-            TS2D_CHECK_CUDA(cudaEventCreate(&b));
-            u->prof_events.push_back({a, b});
-        }
-        TS2D_CHECK_CUDA(cudaEventRecord(u->prof_events[u->prof_used].first, st));
-    }
+    if ((rc = prof_begin(u, st))) return rc;
     if (up.tc) {
         ConvTcParams p;
         int tw, th, tn;
@@ -622,9 +705,10 @@ static int run_up(ts2d_unet *u, UpLayer &up, int N, cudaStream_t st) {
                 u->launches++;
             }
     }
-    if (u->profiling) {
-        TS2D_CHECK_CUDA(cudaEventRecord(u->prof_events[u->prof_used].second, st));
-        u->prof_used++;
+    {
+        const double px = (double)N * up.Hin * up.Win;
+        if ((rc = prof_end(u, up.name, 1, 2.0 * px * up.sh * up.sw * up.cin * up.cout,
+                           (px * up.cin + px * up.sh * up.sw * up.cout) * es, st))) return rc;
     }
     return TS2D_OK;
 }
@@ -781,12 +865,29 @@ extern "C" double ts2d_unet_last_conv_ms(ts2d_unet *u) {
     if (!u || !u->profiling) return -1.0;
     double total = 0.0;
     for (int i = 0; i < u->prof_used; ++i) {
+        if (u->prof_entries[i].kind == 2) continue;     // norm-apply passes are not conv time
         if (cudaEventSynchronize(u->prof_events[i].second) != cudaSuccess) return -1.0;
         float ms = 0.f;
         if (cudaEventElapsedTime(&ms, u->prof_events[i].first, u->prof_events[i].second) != cudaSuccess) return -1.0;
         total += ms;
     }
     return total;
+}
+
+extern "C" int ts2d_unet_profile_count(const ts2d_unet *u) { return (u && u->profiling) ? u->prof_used : 0; }
+
+extern "C" int ts2d_unet_profile_entry(ts2d_unet *u, int i, char *name_out, int name_cap, int *kind, double *ms, double *flops, double *bytes) {
+    TS2D_REQUIRE(u && u->profiling && i >= 0 && i < u->prof_used, "ts2d_unet_profile_entry: no such entry");
+    TS2D_CHECK_CUDA(cudaEventSynchronize(u->prof_events[i].second));
+    float t = 0.f;
+    TS2D_CHECK_CUDA(cudaEventElapsedTime(&t, u->prof_events[i].first, u->prof_events[i].second));
+    const auto &e = u->prof_entries[i];
+    if (name_out && name_cap > 0) { strncpy(name_out, e.name.c_str(), name_cap - 1); name_out[name_cap - 1] = 0; }
+    if (kind) *kind = e.kind;
+    if (ms) *ms = t;
+    if (flops) *flops = e.flops;
+    if (bytes) *bytes = e.bytes;
+    return TS2D_OK;
 }
 
 extern "C" int ts2d_unet_destroy(ts2d_unet *u) {
