@@ -61,6 +61,7 @@ struct ConvLayer {
     bool halo = false;          // conv_halo_kernel (3x3 stride 1, halo tile + resident weights)
     int halo_bn = 0, halo_stages = 0;
     bool halo_maps = false;
+    bool first_fast = false;    // conv_first_kernel (CIN <= 4, 3x3 stride 1, 16-bit activations)
 };
 
 struct UpLayer {
@@ -262,6 +263,26 @@ template <typename T> static int launch_direct(const DirectConvParams &p, int N,
     TS2D_LAUNCH_CHECK();
     return TS2D_OK;
 }
+template <typename T>
+static int launch_first(int cin, const FirstConvParams &p, int N, cudaStream_t st) {
+    const int CG = p.Cout / 16, rows = (256 / CG) / 16;
+    dim3 grid(ceil_div(p.W, 64), ceil_div(p.H, rows * kFirstConvIters), N);
+    const size_t smem = (size_t)(9 * cin * p.Cout + p.Cout + 8 * p.Cout * 2) * sizeof(float);
+    switch (cin) {
+        case 1: conv_first_kernel<T, 1><<<grid, 256, smem, st>>>(p); break;
+        case 2: conv_first_kernel<T, 2><<<grid, 256, smem, st>>>(p); break;
+        case 3: conv_first_kernel<T, 3><<<grid, 256, smem, st>>>(p); break;
+        case 4: conv_first_kernel<T, 4><<<grid, 256, smem, st>>>(p); break;
+        default: set_error("conv_first_kernel: unsupported input channel count %d", cin); return TS2D_ERR_UNSUPPORTED;
+    }
+    TS2D_LAUNCH_CHECK();
+    return TS2D_OK;
+}
+static bool first_fast_eligible(const ts2d_unet_plan &pl, const ConvLayer &c) {
+    return pl.use_tensor_cores && pl.precision != TS2D_PREC_F32 && c.kh == 3 && c.kw == 3 && c.sh == 1 && c.sw == 1 && c.cin <= 4 &&
+           (c.cout == 16 || c.cout == 32 || c.cout == 64) && c.in_ps == c.cin;
+}
+
 static int launch_direct_any(int precision, const DirectConvParams &p, int N, cudaStream_t st) {
     if (precision == TS2D_PREC_F32) return launch_direct<float>(p, N, st);
     if (precision == TS2D_PREC_BF16) return launch_direct<__nv_bfloat16>(p, N, st);
@@ -544,6 +565,7 @@ extern "C" int ts2d_unet_finalize(ts2d_unet *u) {
         c.enc_n = 0;
         c.halo = halo_config(c, c.halo_bn, c.halo_stages);
         c.halo_maps = false;
+        c.first_fast = !c.tc && first_fast_eligible(pl, c);
     }
     for (auto &up : u->ups) {
         up.tc = tc_eligible(pl, up.cin, up.cout, 1, 1, 1, 1, up.Hin, up.Win, up.cin);
@@ -635,6 +657,12 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
             c.enc_n = N;
         }
         rc = is_bf16 ? launch_tc<__nv_bfloat16>(bn, c.kc, c.tmA, c.tmB, p, 1, st) : launch_tc<__half>(bn, c.kc, c.tmA, c.tmB, p, 1, st);
+        if (rc) return rc;
+    } else if (c.first_fast) {
+        FirstConvParams p;
+        memset(&p, 0, sizeof(p));
+        p.in = c.in; p.H = c.Hin; p.W = c.Win; p.w = c.w_direct; p.bias = c.b.dev; p.out = u->raw; p.Cout = c.cout; p.stats = c.stats;
+        rc = is_bf16 ? launch_first<__nv_bfloat16>(c.cin, p, N, st) : launch_first<__half>(c.cin, p, N, st);
         if (rc) return rc;
     } else {
         DirectConvParams p;

@@ -90,6 +90,113 @@ __global__ void __launch_bounds__(128) conv_direct_kernel(const DirectConvParams
 }
 
 // ------------------------------------------------------------------------------------------------------
+// First layer of the network: 3x3 / stride 1 conv with a handful of input channels (CIN <= 4: the 'mean'/'max'
+// projection channels, reference ts2d/tool.py:145-160) and a 16-bit activation type.  K = 9*CIN is far too short
+// for an MMA tile, and the layer is bound by writing its output (64 B per pixel at 32 channels), so it runs on the
+// CUDA cores with a register tile of 4 pixels x 16 output channels per thread (64 fp32 accumulators; each weight
+// fetched from shared memory feeds 4 FMAs).  Block = 256 threads = (256/CG) pixel quads x CG channel groups
+// (CG = Cout/16), covering 64 x rows pixels per iteration, 4 iterations; InstanceNorm sum / sum-of-squares of the
+// ROUNDED outputs leave the block as one double atomic pair per channel.
+// Summation order per output = bias, then taps (r, s) outer, input channel inner: identical to conv_direct_kernel.
+// ------------------------------------------------------------------------------------------------------
+struct FirstConvParams {
+    const void *in; int H, W;          // dense NHWC input [N][H][W][CIN]
+    const float *w;                    // [tap][CIN][Cout] fp32
+    const float *bias;                 // [Cout] or null
+    void *out; int Cout;               // dense NHWC output [N][H][W][Cout]
+    double *stats;                     // [N][Cout][2] or null
+};
+constexpr int kFirstConvIters = 4;
+
+template <typename T, int CIN>
+__global__ void __launch_bounds__(256) conv_first_kernel(const FirstConvParams p) {
+    extern __shared__ float s_first[];           // w [9*CIN][Cout], bias [Cout], reduction scratch [8 warps][Cout][2]
+    const int Cout = p.Cout, CG = Cout >> 4;
+    float *s_w = s_first, *s_b = s_first + 9 * CIN * Cout, *s_red = s_b + Cout;
+    for (int i = threadIdx.x; i < 9 * CIN * Cout; i += 256) s_w[i] = p.w[i];
+    for (int i = threadIdx.x; i < Cout; i += 256) s_b[i] = p.bias ? p.bias[i] : 0.f;
+    __syncthreads();
+    const int cg = threadIdx.x % CG, quad = threadIdx.x / CG;
+    const int rows = (256 / CG) / 16;            // quad rows per iteration
+    const int qx = quad & 15, qy = quad >> 4;
+    const int n = blockIdx.z;
+    const int x0 = blockIdx.x * 64 + qx * 4;
+    const T *in = reinterpret_cast<const T *>(p.in) + (long long)n * p.H * p.W * CIN;
+    T *out = reinterpret_cast<T *>(p.out) + (long long)n * p.H * p.W * Cout + cg * 16;
+    float ssum[16], ssq[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) { ssum[k] = 0.f; ssq[k] = 0.f; }
+    for (int it = 0; it < kFirstConvIters; ++it) {
+        const int y = (blockIdx.y * kFirstConvIters + it) * rows + qy;
+        if (y >= p.H || x0 >= p.W) continue;
+        float xin[3][6][CIN];
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+            const int iy = y + r - 1;
+#pragma unroll
+            for (int c = 0; c < 6; ++c) {
+                const int ix = x0 + c - 1;
+                const bool inb = iy >= 0 && iy < p.H && ix >= 0 && ix < p.W;
+#pragma unroll
+                for (int ci = 0; ci < CIN; ++ci) xin[r][c][ci] = inb ? to_f32<T>(in[((long long)iy * p.W + ix) * CIN + ci]) : 0.f;
+            }
+        }
+        float acc[4][16];
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int k = 0; k < 16; ++k) acc[j][k] = s_b[cg * 16 + k];
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+#pragma unroll
+            for (int s = 0; s < 3; ++s)
+#pragma unroll
+                for (int ci = 0; ci < CIN; ++ci) {
+                    const float4 *wp = reinterpret_cast<const float4 *>(s_w + ((r * 3 + s) * CIN + ci) * Cout + cg * 16);
+                    float wv[16];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) { const float4 t = wp[q]; wv[4 * q] = t.x; wv[4 * q + 1] = t.y; wv[4 * q + 2] = t.z; wv[4 * q + 3] = t.w; }
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+#pragma unroll
+                        for (int k = 0; k < 16; ++k) acc[j][k] = fmaf(xin[r][j + s][ci], wv[k], acc[j][k]);
+                }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            if (x0 + j >= p.W) continue;
+            alignas(16) T rv[16];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                rv[k] = from_f32<T>(acc[j][k]);
+                const float rf = to_f32<T>(rv[k]);
+                ssum[k] += rf; ssq[k] += rf * rf;
+            }
+            uint4 *dst = reinterpret_cast<uint4 *>(out + ((long long)y * p.W + x0 + j) * Cout);
+            dst[0] = *reinterpret_cast<const uint4 *>(&rv[0]);
+            dst[1] = *reinterpret_cast<const uint4 *>(&rv[8]);
+        }
+    }
+    if (p.stats) {
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            for (int o = 16; o >= CG; o >>= 1) {           // lanes that share this channel group
+                ssum[k] += __shfl_xor_sync(0xffffffffu, ssum[k], o);
+                ssq[k] += __shfl_xor_sync(0xffffffffu, ssq[k], o);
+            }
+            if (lane < CG) { s_red[(warp * Cout + cg * 16 + k) * 2] = ssum[k]; s_red[(warp * Cout + cg * 16 + k) * 2 + 1] = ssq[k]; }
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < Cout * 2; i += 256) {
+            double t = 0.0;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) t += (double)s_red[w * Cout * 2 + i];
+            atomicAdd(p.stats + (long long)n * Cout * 2 + i, t);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
 // InstanceNorm2d(affine, biased variance over H*W per (n,c)) + LeakyReLU, from the epilogue statistics.
 // raw: dense [N][HW][C]; out: [N][HW] pixels with stride out_ps (may be a channel slice of a concat buffer).
 // ------------------------------------------------------------------------------------------------------
