@@ -91,6 +91,43 @@ __device__ __forceinline__ void tcgen05_mma_f16(uint32_t tmem_d, uint64_t adesc,
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
         "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
+// ---- warp-uniform MMA issue -------------------------------------------------------------------------------------
+// The MMA warp runs its loop CONVERGENTLY (all 32 lanes wait on the barriers and compute the descriptors, which
+// the compiler then keeps in uniform registers); only the tcgen05 instructions are predicated on one elected lane.
+// Issuing from inside an `if (lane == 0)` region instead makes every descriptor a per-thread value and costs a
+// R2UR "waterfall" loop plus ~20 scalar instructions per MMA (measured: ~100 cycles per N=32 MMA that needs 16).
+__device__ __forceinline__ uint32_t elect_one() {
+    uint32_t pred;
+    asm volatile("{\n.reg .pred P;\nelect.sync _|P, 0xffffffff;\nselp.u32 %0, 1, 0, P;\n}" : "=r"(pred));
+    return pred;
+}
+// descriptor = {lo, hi}: lo = start address >> 4 (14 bits) | LBO field, hi = SBO | version | swizzle mode (constant per operand)
+__device__ __forceinline__ void tcgen05_mma_f16_lohi(uint32_t leader, uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                                     uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p, q;\n"
+        ".reg .b64 da, db;\n"
+        "setp.ne.b32 q, %0, 0;\n"
+        "setp.ne.b32 p, %7, 0;\n"
+        "mov.b64 da, {%2, %3};\n"
+        "mov.b64 db, {%4, %5};\n"
+        "@q tcgen05.mma.cta_group::1.kind::f16 [%1], da, db, %6, p;\n"
+        "}\n" ::"r"(leader), "r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tcgen05_commit_pred(uint32_t leader, uint64_t *bar) {
+    asm volatile(
+        "{\n"
+        ".reg .pred q;\n"
+        "setp.ne.b32 q, %0, 0;\n"
+        "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%1];\n"
+        "}\n" ::"r"(leader), "r"(smem_u32(bar)) : "memory");
+}
+template <int KC> __device__ __forceinline__ uint32_t desc_lo(uint32_t saddr) { return ((saddr >> 4) & 0x3FFFu) | (1u << 16); }
+template <int KC> __device__ __forceinline__ constexpr uint32_t desc_hi(uint32_t sbo_bytes) {
+    return ((sbo_bytes >> 4) & 0x3FFFu) | (1u << 14) | ((KC == 64 ? 2u : 4u) << 29);
+}
+
 __device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
@@ -232,35 +269,32 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer =====================
-        if (lane == 0) {
-            const uint32_t idesc = make_idesc<DT>(BN);
-            int stage = 0;
-            uint32_t phase = 0;
-            int it = 0;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-                const int buf = it & 1;
-                const uint32_t use = (uint32_t)(it >> 1);
-                mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);
+        // ===================== MMA issuer (whole warp convergent, one elected lane issues) =====================
+        const uint32_t leader = elect_one();
+        const uint32_t idesc = make_idesc<DT>(BN);
+        constexpr uint32_t hi = desc_hi<KC>(KC == 64 ? 1024 : 512);
+        const uint32_t s0_lo = desc_lo<KC>(smem_u32(smem));
+        int stage = 0;
+        uint32_t phase = 0;
+        int it = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+            const int buf = it & 1;
+            const uint32_t use = (uint32_t)(it >> 1);
+            mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);
+            tcgen05_fence_after();
+            const uint32_t d_tmem = tmem_base + (uint32_t)(buf * BN);
+            for (int kc = 0; kc < k_chunks; ++kc) {
+                mbar_wait(&full_bar[stage], phase);
                 tcgen05_fence_after();
-                const uint32_t d_tmem = tmem_base + (uint32_t)(buf * BN);
-                for (int kc = 0; kc < k_chunks; ++kc) {
-                    mbar_wait(&full_bar[stage], phase);
-                    tcgen05_fence_after();
-                    const uint32_t sa = smem_u32(smem + stage * kStageBytes);
-                    const uint32_t sb = sa + kABytes;
-                    const uint64_t adesc = make_smem_desc<KC>(sa);
-                    const uint64_t bdesc = make_smem_desc<KC>(sb);
+                const uint32_t a_lo = s0_lo + (uint32_t)(stage * (kStageBytes >> 4));
+                const uint32_t b_lo = a_lo + (uint32_t)(kABytes >> 4);
 #pragma unroll
-                    for (int k = 0; k < KC / 16; ++k) {
-                        // advance 16 elements = 32 bytes along K inside the swizzled row: +2 in the (addr>>4) field
-                        tcgen05_mma_f16(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kc | k) ? 1u : 0u);
-                    }
-                    tcgen05_commit(&empty_bar[stage]);       // frees the smem slot once these MMAs retire
-                    if (++stage == kStages) { stage = 0; phase ^= 1; }
-                }
-                tcgen05_commit(&tmem_full[buf]);             // accumulator complete
+                for (int k = 0; k < KC / 16; ++k)   // 16 elements = 32 bytes along K inside the swizzled row: +2 in the (addr >> 4) field
+                    tcgen05_mma_f16_lohi(leader, d_tmem, a_lo + (uint32_t)(k * 2), hi, b_lo + (uint32_t)(k * 2), hi, idesc, k ? 1u : (uint32_t)(kc != 0));
+                tcgen05_commit_pred(leader, &empty_bar[stage]);       // frees the smem slot once these MMAs retire
+                if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
+            tcgen05_commit_pred(leader, &tmem_full[buf]);             // accumulator complete
         }
     } else {
         // ===================== epilogue (warps 2..5) =====================

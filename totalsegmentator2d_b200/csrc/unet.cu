@@ -219,7 +219,7 @@ static int launch_halo_inst(const CUtensorMap &tmA, const CUtensorMap &tmB, cons
     const int n_tiles_n = p.Cout / BN;
     const int total = p.tiles_x * p.tiles_y * p.N;
     const int gx = std::max(1, std::min(total, kNumSMs / n_tiles_n));
-    conv_halo_kernel<BN, KC, DT, FUSE><<<dim3(gx, n_tiles_n), FUSE ? 320 : 192, smem, st>>>(tmA, tmB, p);
+    conv_halo_kernel<BN, KC, DT, FUSE><<<dim3(gx, n_tiles_n), FUSE ? 448 : 320, smem, st>>>(tmA, tmB, p);
     TS2D_LAUNCH_CHECK();
     return TS2D_OK;
 }
