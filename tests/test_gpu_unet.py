@@ -111,3 +111,25 @@ def test_errors_are_loud():
         p.predict_logits_from_preprocessed_data(torch.zeros(2, 16, 16))
     with pytest.raises(L.TS2DError):
         _make([8, 16], (17, 17))                      # patch not divisible by the strides
+
+
+@pytest.mark.parametrize("precision", ["bf16", "fp16"])
+def test_deferred_norm_is_bit_identical(precision, monkeypatch):
+    """conv_halo_kernel<FUSE> (producer's InstanceNorm + LeakyReLU applied on the consumer's halo in shared memory) and the
+    blend kernel's in-line normalisation of the last decoder conv must reproduce the materialised norm_act_kernel path
+    bit for bit: per-tile logits, blended logits and masks."""
+    dt = torch.bfloat16 if precision == "bf16" else torch.float16
+    outs = []
+    for fuse in ("0", "2"):
+        monkeypatch.setenv("TS2D_FUSE_NORM", fuse)
+        p, sd, spec = _make([32, 64, 128, 128], (64, 96), heads=6, precision=precision, seed=11)
+        x, xd = _tiles(4, 2, (64, 96), 9, dt)
+        tile_logits = p.predict_tile_logits(xd).cpu()
+        mid = p.forward_debug(xd, "enc1.1", (64, 32, 48)).cpu()
+        g = torch.Generator().manual_seed(4)
+        data = torch.randn(2, 1, 100, 130, generator=g)
+        blended = p.predict_logits_from_preprocessed_data(data).cpu()
+        outs.append((tile_logits, mid, blended))
+        p.close()
+    for a, b in zip(*outs):
+        assert torch.equal(a, b)

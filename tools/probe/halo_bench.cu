@@ -39,10 +39,11 @@ __global__ void fill_kernel(__nv_bfloat16 *p, size_t n, uint32_t seed) {
 }
 
 struct Layer { const char *name; int N, H, W, Cin, Cout; };
+static double *g_in_stats = nullptr;   // [N][Cin][2]: sum 0, sum of squares HW -> mean 0, var 1
 
-template <int BN, int KC>
+template <int BN, int KC, bool FUSE = false>
 static float run(const Layer &L, int stages, int dbg, bool timing, int reps, __nv_bfloat16 *in, __nv_bfloat16 *w, __nv_bfloat16 *out, float *bias,
-                 double *stats, unsigned long long *dbg_out, double *waits /*[4] avg cycles*/) {
+                 double *stats, unsigned long long *dbg_out, double *waits /*[8] avg cycles*/) {
     CUtensorMap tmA, tmB;
     {
         cuuint64_t dims[4] = {(cuuint64_t)L.Cin, (cuuint64_t)L.W, (cuuint64_t)L.H, (cuuint64_t)L.N};
@@ -62,9 +63,10 @@ static float run(const Layer &L, int stages, int dbg, bool timing, int reps, __n
     p.tiles_x = (L.W + 7) / 8; p.tiles_y = (L.H + 15) / 16; p.n_stages = stages;
     p.out_ps = L.Cout; p.out = out; p.bias = bias; p.stats = stats; p.Cin = L.Cin;
     p.dbg = dbg; p.dbg_out = timing ? dbg_out : nullptr;
+    if (FUSE) { p.in_stats = g_in_stats; p.in_gamma = nullptr; p.in_beta = nullptr; p.in_hw = L.H * L.W; p.in_eps = 1e-5f; p.in_slope = 0.01f; }
     const int wbytes = ((9 * L.Cin * BN * 2) + 1023) & ~1023;
-    const int smem = 1024 + wbytes + stages * halo_stage_bytes<KC>() + 512 + BN * 4 + 64;
-    CK(cudaFuncSetAttribute(conv_halo_kernel<BN, KC, __nv_bfloat16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
+    const int smem = 1024 + wbytes + stages * halo_stage_bytes<KC>() + kHaloTailBytes;
+    CK(cudaFuncSetAttribute(conv_halo_kernel<BN, KC, __nv_bfloat16, FUSE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
     const int nt = L.Cout / BN;
     const int total = p.tiles_x * p.tiles_y * p.N;
     const int gx = std::max(1, std::min(total, 148 / nt));
@@ -74,7 +76,7 @@ static float run(const Layer &L, int stages, int dbg, bool timing, int reps, __n
     for (int r = 0; r < reps + 2; ++r) {
         CK(cudaMemsetAsync(stats, 0, (size_t)L.N * L.Cout * 2 * sizeof(double)));
         CK(cudaEventRecord(e0));
-        conv_halo_kernel<BN, KC, __nv_bfloat16, false><<<dim3(gx, nt), 320, smem>>>(tmA, tmB, p);
+        conv_halo_kernel<BN, KC, __nv_bfloat16, FUSE><<<dim3(gx, nt), kHaloThreads, smem>>>(tmA, tmB, p);
         CK(cudaEventRecord(e1));
         CK(cudaEventSynchronize(e1));
         CK(cudaGetLastError());
@@ -83,9 +85,9 @@ static float run(const Layer &L, int stages, int dbg, bool timing, int reps, __n
     }
     std::sort(ms.begin(), ms.end());
     if (timing && waits) {
-        std::vector<unsigned long long> h((size_t)gx * nt * 4);
+        std::vector<unsigned long long> h((size_t)gx * nt * 8);
         CK(cudaMemcpy(h.data(), dbg_out, h.size() * 8, cudaMemcpyDeviceToHost));
-        for (int k = 0; k < 4; ++k) { double s = 0; for (int c = 0; c < gx * nt; ++c) s += (double)h[(size_t)c * 4 + k]; waits[k] = s / (gx * nt); }
+        for (int k = 0; k < 8; ++k) { double s = 0; for (int c = 0; c < gx * nt; ++c) s += (double)h[(size_t)c * 8 + k]; waits[k] = s / (gx * nt); }
     }
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     return ms[ms.size() / 2];
@@ -113,37 +115,49 @@ int main(int argc, char **argv) {
     __nv_bfloat16 *in, *out, *w;
     float *bias; double *stats; unsigned long long *dbg_out;
     CK(cudaMalloc(&in, max_in * 2)); CK(cudaMalloc(&out, max_out * 2)); CK(cudaMalloc(&w, (size_t)9 * 128 * 128 * 2));
-    CK(cudaMalloc(&bias, 128 * 4)); CK(cudaMalloc(&stats, (size_t)12 * 128 * 2 * 8)); CK(cudaMalloc(&dbg_out, 148 * 4 * 8));
+    CK(cudaMalloc(&bias, 128 * 4)); CK(cudaMalloc(&stats, (size_t)12 * 128 * 2 * 8)); CK(cudaMalloc(&dbg_out, 148 * 8 * 8)); CK(cudaMemset(dbg_out, 0, 148 * 8 * 8));
     fill_kernel<<<1184, 256>>>(in, max_in, 1u);
     fill_kernel<<<64, 256>>>(w, (size_t)9 * 128 * 128, 7u);
     CK(cudaMemset(bias, 0, 128 * 4));
     CK(cudaDeviceSynchronize());
-    const int dbgs[] = {0, 1, 2, 3, 4, 7, 8, 15};
-    printf("dbg bits: 1 no stats, 2 no stores, 4 tap 0 only, 8 all halos = tile 0 (L2 hits)\n");
+    {
+        std::vector<double> h((size_t)12 * 128 * 2);
+        for (size_t i = 0; i < h.size(); i += 2) { h[i] = 0.0; h[i + 1] = 512.0 * 512.0; }
+        CK(cudaMalloc(&g_in_stats, h.size() * 8));
+        CK(cudaMemcpy(g_in_stats, h.data(), h.size() * 8, cudaMemcpyHostToDevice));
+    }
+    const int dbgs[] = {0, 16, 16 + 32, 16 + 64, 16 + 32 + 64, 16 + 3};   // bit 16 (harness only): FUSE variant
+    printf("dbg bits: 1 no stats, 2 no stores, 4 tap 0 only, 8 all halos = tile 0 (L2 hits), 16 FUSE (deferred InstanceNorm on the halo)\n");
     for (const Layer &L : layers) {
         const int kc = L.Cin % 64 == 0 ? 64 : 32;
         const int bn = L.Cout % 64 == 0 ? 64 : 32;
         int stages = 6;
-        auto smem_of = [&](int st) { return 1024 + (((9 * L.Cin * bn * 2) + 1023) & ~1023) + st * (kc == 64 ? halo_stage_bytes<64>() : halo_stage_bytes<32>()) + 512 + bn * 4 + 64; };
+        auto smem_of = [&](int st) { return 1024 + (((9 * L.Cin * bn * 2) + 1023) & ~1023) + st * (kc == 64 ? halo_stage_bytes<64>() : halo_stage_bytes<32>()) + kHaloTailBytes; };
         while (stages > 2 && smem_of(stages) > 225 * 1024) --stages;
         const double flops = 2.0 * L.N * L.H * L.W * 9.0 * L.Cin * L.Cout;
         const double bytes = 2.0 * L.N * L.H * L.W * (L.Cin + L.Cout);
         const double tiles_per_cta = (double)((L.W + 7) / 8) * ((L.H + 15) / 16) * L.N / (148 / (L.Cout / bn));
         printf("%s  BN=%d KC=%d stages=%d  tiles/CTA %.1f\n", L.name, bn, kc, stages, tiles_per_cta);
         for (int dbg : dbgs) {
-            double waits[4] = {0, 0, 0, 0};
+            double waits[8] = {0, 0, 0, 0, 0, 0, 0, 0};
             float ms = 0.f;
             for (int timing = 0; timing < 2; ++timing) {
                 float t;
-                if (bn == 32 && kc == 32) t = run<32, 32>(L, stages, dbg, timing, 5, in, w, out, bias, stats, dbg_out, waits);
-                else if (bn == 32 && kc == 64) t = run<32, 64>(L, stages, dbg, timing, 5, in, w, out, bias, stats, dbg_out, waits);
-                else if (bn == 64 && kc == 32) t = run<64, 32>(L, stages, dbg, timing, 5, in, w, out, bias, stats, dbg_out, waits);
-                else t = run<64, 64>(L, stages, dbg, timing, 5, in, w, out, bias, stats, dbg_out, waits);
+                const int d = dbg & ~16;
+                if (dbg & 16) {
+                    if (bn == 32 && kc == 32) t = run<32, 32, true>(L, stages, d, timing, 5, in, w, out, bias, stats, dbg_out, waits);
+                    else if (bn == 32 && kc == 64) t = run<32, 64, true>(L, stages, d, timing, 5, in, w, out, bias, stats, dbg_out, waits);
+                    else if (bn == 64 && kc == 32) t = run<64, 32, true>(L, stages, d, timing, 5, in, w, out, bias, stats, dbg_out, waits);
+                    else t = run<64, 64, true>(L, stages, d, timing, 5, in, w, out, bias, stats, dbg_out, waits);
+                } else if (bn == 32 && kc == 32) t = run<32, 32>(L, stages, d, timing, 5, in, w, out, bias, stats, dbg_out, waits);
+                else if (bn == 32 && kc == 64) t = run<32, 64>(L, stages, d, timing, 5, in, w, out, bias, stats, dbg_out, waits);
+                else if (bn == 64 && kc == 32) t = run<64, 32>(L, stages, d, timing, 5, in, w, out, bias, stats, dbg_out, waits);
+                else t = run<64, 64>(L, stages, d, timing, 5, in, w, out, bias, stats, dbg_out, waits);
                 if (!timing) ms = t;
             }
-            printf("  dbg=%2d  %8.4f ms  %7.1f TF/s  %6.0f GB/s | cycles/CTA %9.0f (%.0f per tile, clock %.2f GHz)  mma-wait-halo %4.1f%%  mma-wait-tmem %4.1f%%  epi-wait %4.1f%%\n",
+            printf("  dbg=%2d  %8.4f ms  %7.1f TF/s  %6.0f GB/s | cycles/CTA %9.0f (%.0f per tile, clock %.2f GHz)  mma-wait-halo %4.1f%%  mma-wait-tmem %4.1f%%  epi-wait %4.1f%%  xform-wait %4.1f%% xform-work %4.1f%%\n",
                    dbg, ms, flops / ms / 1e9, bytes / ms / 1e6, waits[0], waits[0] / tiles_per_cta, waits[0] / (ms * 1e6), 100 * waits[1] / waits[0],
-                   100 * waits[2] / waits[0], 100 * waits[3] / waits[0]);
+                   100 * waits[2] / waits[0], 100 * waits[3] / waits[0], 100 * waits[4] / waits[0], 100 * waits[5] / waits[0]);
         }
     }
     return 0;

@@ -16,12 +16,22 @@
 //   weights  = all 9 taps x Cin x BN of the CTA's output-channel block stay resident in shared memory for the
 //              whole persistent loop (loaded once per CTA): per tile only the halo moves.
 //
-// Optional fused InstanceNorm-apply + LeakyReLU of the PRODUCER layer on the A operand ("deferred norm"): four
-// transform warps rewrite the halo in place (y = leaky(x*scale[n][c] + shift[n][c]), 0 outside the image) between
-// the TMA arrival and the MMAs, so the normalised tensor is never written to or read from HBM.
+// Measured on B200 (tools/probe/mma_rate.cu): one M=128, K=16 tcgen05.mma costs ~45 cycles at N=32 and ~51 at N=64
+// (the N/2-cycle floor only shows from N=128 on), so these layers are bound by the NUMBER of MMAs (9 taps x Cin/16
+// per tile); everything else - TMA, the operand transform, the epilogue - must stay off that critical path.
 //
-// Warp roles: warp 0 TMA producer, warp 1 TMEM alloc + MMA issuer, warps 2-9 epilogue (two groups of four, one per TMEM
-// accumulator buffer: TMEM -> +bias -> round -> InstanceNorm sum/sumsq -> global), warps 10-13 halo transform (only when FUSE).
+// Deferred normalisation (FUSE): the input is the PRODUCER conv's raw output; its InstanceNorm + LeakyReLU are applied
+// to the halo in shared memory between the TMA arrival and the MMAs (y = leaky(x*scale[n][c] + shift[n][c]), zeros
+// outside the image stay zeros = the conv padding of the normalised tensor), so the normalised tensor is never
+// written to or read from HBM.  Same arithmetic as norm_act_kernel: the two paths are bit-identical.
+//
+// Warp roles (384 threads): warp 0 TMA producer, warp 1 TMEM alloc + MMA issuer (whole warp convergent, one elected
+// lane issues), warps 2-3 idle, warps 4-11 = 8 WORKER warps.  A worker alternates between two duties, both of which
+// are latency bound when left to one warp per scheduler:
+//   transform (FUSE)  all 256 worker threads rewrite the halo of tile j (16-byte chunks, loads batched before math);
+//   epilogue          TMEM -> +bias -> round -> per-thread InstanceNorm partial sums -> 32-byte global stores, for
+//                     tile j - kLag.  BN == 32: the two worker warpgroups alternate tiles (group g owns TMEM buffer
+//                     g); BN == 64: both work on every tile, one half of the columns each.
 #pragma once
 #include "conv_tc.cuh"
 
@@ -37,42 +47,42 @@ struct ConvHaloParams {
     void *out;
     const float *bias;          // [Cout] or null
     double *stats;              // [Nmax][Cout][2] or null  (sum, sum of squares of the ROUNDED outputs)
-    // fused input transform (FUSE only): per (image, input channel) scale / shift, LeakyReLU slope per channel
-    const float *in_scale;      // [Nmax][Cin]
-    const float *in_shift;      // [Nmax][Cin]
-    const float *in_slope;      // [Cin]   (1.0 = no activation, e.g. the transposed-conv half of a concat buffer)
+    // fused input transform (FUSE only)
+    const double *in_stats;     // [Nmax][Cin][2] sum / sum of squares over the in_hw pixels of (image, channel)
+    const float *in_gamma;      // [Cin] or null
+    const float *in_beta;       // [Cin] or null
+    int in_hw;                  // pixels per image of the producer's output
+    float in_eps, in_slope;
     int Cin;
     // diagnostics (tools/probe/halo_bench.cu only; 0 in the product): knock-out bits
-    //   1 = no InstanceNorm statistics, 2 = no global stores, 4 = only tap 0 is multiplied, 8 = every halo is tile 0's (L2 hits)
+    //   1 = no InstanceNorm statistics, 2 = no global stores, 4 = only tap 0 is multiplied, 8 = every halo is tile 0's (L2 hits),
+    //   32 = transform without the proxy fence (WRONG results, timing only), 64 = transform does no loads / math / stores
     int dbg;
-    unsigned long long *dbg_out;   // [gridDim.x*gridDim.y][4]: cycles total / MMA-issuer waits on halo / on TMEM / epilogue waits
+    unsigned long long *dbg_out;   // [gridDim.x*gridDim.y][8] cycles: total / MMA waits on halo / MMA waits on TMEM / epilogue waits / transform waits / transform work
 };
 
 constexpr int kHaloW = 10, kHaloH = 18, kHaloPix = kHaloW * kHaloH;
+constexpr int kHaloThreads = 384;
+constexpr int kHaloWorkers = 256;
 
 template <int KC> constexpr int halo_stage_bytes() { return ((kHaloPix * KC * 2 + 1023) / 1024) * 1024; }
+// bytes after the halo ring: barriers (512) + bias [64] + scale/shift table [2][Cin <= 256]
+constexpr int kHaloTailBytes = 512 + 64 * 4 + 2 * 256 * 4;
 
-template <int KC>
-__device__ __forceinline__ uint64_t make_smem_desc_sbo(uint32_t saddr, uint32_t sbo_bytes) {
-    constexpr uint64_t layout = (KC == 64) ? 2ull /*SWIZZLE_128B*/ : 4ull /*SWIZZLE_64B*/;
-    uint64_t d = 0;
-    d |= (uint64_t)((saddr >> 4) & 0x3FFF);
-    d |= (uint64_t)1 << 16;
-    d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
-    d |= (uint64_t)1 << 46;
-    d |= layout << 61;
-    return d;
-}
+__device__ __forceinline__ void named_bar_sync(int id, int threads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory"); }
 
 template <int BN, int KC, typename DT, bool FUSE>
-__global__ void __launch_bounds__(FUSE ? 448 : 320, 1)
+__global__ void __launch_bounds__(kHaloThreads, 1)
 conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const ConvHaloParams p) {
+    static_assert(BN == 32 || BN == 64, "conv_halo_kernel: BN must be 32 or 64");
     constexpr int kRowB = KC * 2;                      // bytes per pixel row of the operand
     constexpr int kHaloBytes = kHaloPix * kRowB;       // bytes TMA delivers per halo
     constexpr int kStageBytes = halo_stage_bytes<KC>();
-    constexpr int kWBlock = BN * kRowB;                // one (tap, cin chunk) weight block
+    constexpr int kWBlock = BN * kRowB;                // one (cin chunk, tap) weight block
     constexpr int kTmemCols = TcCfg<BN>::kTmemCols;
     constexpr int kMaxStages = 8;
+    constexpr bool kSplit = BN > 32;                   // both worker groups on every tile (column halves) vs alternating tiles
+    constexpr int kLag = FUSE ? 2 : 0;                 // a worker runs the epilogue of tile j - kLag after the transform of tile j
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -86,7 +96,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     uint64_t *tmem_empty = tmem_full + 2;             // [2]
     uint64_t *w_bar = tmem_empty + 2;
     uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(w_bar + 1);
-    float *s_bias = reinterpret_cast<float *>(reinterpret_cast<uint8_t *>(full_bar) + 256);     // [BN], 16-byte aligned
+    float *s_bias = reinterpret_cast<float *>(reinterpret_cast<uint8_t *>(full_bar) + 512);     // [64]
+    float *s_ss = s_bias + 64;                                                                   // [2][Cin]: scale, shift of the current image
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -95,8 +106,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
-        for (int s = 0; s < p.n_stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); mbar_init(&ready_bar[s], 128); }
-        for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], BN > 32 ? 256 : 128); }
+        for (int s = 0; s < p.n_stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); mbar_init(&ready_bar[s], kHaloWorkers); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], kSplit ? 256 : 128); }
         mbar_init(w_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -104,8 +115,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr)), "n"(kTmemCols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
-    if (warp >= 2 && warp < 6)
-        for (int i = threadIdx.x - 64; i < BN; i += 128) s_bias[i] = p.bias ? p.bias[blockIdx.y * BN + i] : 0.f;
+    if (warp >= 4)
+        for (int i = threadIdx.x - 128; i < BN; i += kHaloWorkers) s_bias[i] = p.bias ? p.bias[blockIdx.y * BN + i] : 0.f;
     tcgen05_fence_before();
     __syncthreads();
     tcgen05_fence_after();
@@ -124,8 +135,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // ===================== TMA producer =====================
         if (lane == 0) {
             mbar_expect_tx(w_bar, (uint32_t)w_bytes);
-            for (int tap = 0; tap < 9; ++tap)
-                for (int cc = 0; cc < p.cin_chunks; ++cc)
+            for (int cc = 0; cc < p.cin_chunks; ++cc)
+                for (int tap = 0; tap < 9; ++tap)
                     tma_load_3d(smem_w + (cc * 9 + tap) * kWBlock, &tmB, w_bar, cc * KC, nt * BN, tap);
             int stage = 0;
             uint32_t phase = 0;
@@ -185,18 +196,13 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             tcgen05_commit_pred(leader, &tmem_full[buf]);
         }
         if (p.dbg_out && leader) {
-            unsigned long long *o = p.dbg_out + (size_t)(blockIdx.y * gridDim.x + blockIdx.x) * 4;
+            unsigned long long *o = p.dbg_out + (size_t)(blockIdx.y * gridDim.x + blockIdx.x) * 8;
             o[0] = (unsigned long long)(clock64() - t_start); o[1] = (unsigned long long)w_halo; o[2] = (unsigned long long)w_tmem;
         }
-    } else if (warp < 10) {
-        // ===================== epilogue: two groups of 4 warps (warps 2..5, warps 6..9), 32 accumulator columns per warp =====================
-        // One warp per TMEM lane quarter is latency bound (~900 cycles per 32 columns), so the work is spread over 8 warps:
-        //   BN == 32: the groups alternate tiles (group g owns TMEM buffer g), the epilogue of tile i overlaps that of tile i-1;
-        //   BN == 64: both groups work on every tile, each on one half of the columns (register budget: 2*32 statistics
-        //             accumulators per thread either way; 10 warps are allocated as 12, i.e. 168 registers per thread).
-        constexpr bool kSplit = BN > 32;
-        static_assert(BN == 32 || BN == 64, "conv_halo_kernel: BN must be 32 or 64");
-        const int grp = (warp - 2) >> 2;
+    } else if (warp >= 4) {
+        // ===================== workers (warps 4..11): halo transform of tile j, then epilogue of tile j - kLag =====================
+        const int wt = threadIdx.x - 128;       // 0..255
+        const int grp = wt >> 7;                // worker warpgroup
         const int q = warp & 3;                 // TMEM lane quarter this warp may access
         const int row = q * 32 + lane;
         const int ix = row & 7, iy = row >> 3;
@@ -205,7 +211,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const bool do_stats = p.stats != nullptr && !(p.dbg & 1);
         // InstanceNorm statistics: every thread keeps running sums of ITS pixel row for its 32 channels across the tiles of
         // one image (no cross-lane traffic per tile); the 32-lane transpose-reduction and the double atomics happen only
-        // when the image changes (a CTA walks the images in order: <= N flushes).
+        // when the image changes (<= 3 flushes per CTA with the contiguous partition).
         float tacc1[32], tacc2[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) { tacc1[i] = 0.f; tacc2[i] = 0.f; }
@@ -220,19 +226,113 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             atomicAdd(s, (double)s1);
             atomicAdd(s + 1, (double)s2);
         };
-        float bias_r[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) bias_r[j] = s_bias[col0 + j];
         int cur_n = -1;
-        long long w_epi = 0;
-        // tile walker: coordinates advance with carries, no divisions in the loop
-        const int step = kSplit ? 1 : 2;
-        const int sx = step % p.tiles_x, sy = (step / p.tiles_x) % p.tiles_y, sn = step / tiles_per_img;
-        int tile = t_begin + (kSplit ? 0 : grp);
-        int tx = tile % p.tiles_x, ty = (tile / p.tiles_x) % p.tiles_y, n = tile / tiles_per_img + p.n_base;
-        for (uint32_t k = 0; tile < t_end; tile += step, ++k) {
-            const int buf = kSplit ? (int)(k & 1) : grp;
-            const uint32_t par = kSplit ? ((k >> 1) & 1) : (k & 1);
+        long long w_epi = 0, x_wait = 0, x_work = 0;
+        // epilogue tile walker (coordinates advance with carries, no divisions in the loop)
+        const int estep = kSplit ? 1 : 2;
+        const int esx = estep % p.tiles_x, esy = (estep / p.tiles_x) % p.tiles_y, esn = estep / tiles_per_img;
+        int e_tile = t_begin + (kSplit ? 0 : grp);
+        int tx = e_tile % p.tiles_x, ty = (e_tile / p.tiles_x) % p.tiles_y, n = e_tile / tiles_per_img + p.n_base;
+        // transform state
+        constexpr int kCpp = KC / 8;                                             // 16-byte chunks (8 channels) per halo pixel
+        constexpr int kIters = (kHaloPix * kCpp + kHaloWorkers - 1) / kHaloWorkers;     // chunks per thread per halo: 3 (KC=32) or 6 (KC=64)
+        constexpr int kBatch = 3;
+        constexpr uint32_t kXorMask = (KC == 64) ? 7u : 3u;
+        const int cb = wt % kCpp;                                                // 256 % kCpp == 0: a thread keeps ONE channel block
+        // tile-invariant per-chunk data: byte offset inside a stage (absolute-address swizzle: the stage base is 1024-byte
+        // aligned, so chunk index XOR ((row offset >> 7) & mask)) | halo x << 16 | halo y << 20
+        uint32_t meta[kIters];
+#pragma unroll
+        for (int i = 0; i < kIters; ++i) {
+            const int pix = (wt + i * kHaloWorkers) / kCpp;
+            const uint32_t row_off = (uint32_t)(pix * kRowB);
+            const uint32_t sw = (row_off >> 7) & kXorMask;
+            meta[i] = pix < kHaloPix ? ((row_off + (((uint32_t)cb ^ sw) << 4)) | ((uint32_t)(pix % kHaloW) << 16) | ((uint32_t)(pix / kHaloW) << 20)) : 0xFFFFFFFFu;
+        }
+        int xtx = t_begin % p.tiles_x, xty = (t_begin / p.tiles_x) % p.tiles_y, xn = t_begin / tiles_per_img + p.n_base;
+        int xf_n = -1, xstage = 0;
+        uint32_t xphase = 0;
+        const float slope = p.in_slope;
+
+        const int n_local = t_end - t_begin;
+        for (int j = 0; j < n_local + kLag; ++j) {
+            if (FUSE && j < n_local) {
+                // ---------------- transform the halo(s) of local tile j ----------------
+                if (xn != xf_n) {
+                    // scale / shift of the producer's InstanceNorm for image xn, all Cin channels: same arithmetic as norm_act_kernel
+                    // (double mean / rstd, one rounding to float), once per image and CTA
+                    named_bar_sync(1, kHaloWorkers);
+                    for (int c = wt; c < p.Cin; c += kHaloWorkers) {
+                        const double *st = p.in_stats + ((long long)xn * p.Cin + c) * 2;
+                        const double mean = st[0] / (double)p.in_hw;
+                        const double var = fmax(st[1] / (double)p.in_hw - mean * mean, 0.0);
+                        const double rstd = 1.0 / sqrt(var + (double)p.in_eps);
+                        const float g = p.in_gamma ? __ldg(p.in_gamma + c) : 1.f, b = p.in_beta ? __ldg(p.in_beta + c) : 0.f;
+                        s_ss[c] = (float)(rstd * (double)g);
+                        s_ss[p.Cin + c] = (float)((double)b - mean * rstd * (double)g);
+                    }
+                    named_bar_sync(1, kHaloWorkers);
+                    xf_n = xn;
+                }
+                // halo pixel (hx, hy) is image pixel (xtx*8 - 1 + hx, xty*16 - 1 + hy)
+                const int hx_lo = 1 - xtx * 8, hx_hi = p.W + 1 - xtx * 8, hy_lo = 1 - xty * 16, hy_hi = p.H + 1 - xty * 16;
+                for (int cc = 0; cc < p.cin_chunks; ++cc) {
+                    float scs[8], shs[8];
+                    {
+                        const float4 *ps = reinterpret_cast<const float4 *>(s_ss + cc * KC + cb * 8);
+                        const float4 *ph = reinterpret_cast<const float4 *>(s_ss + p.Cin + cc * KC + cb * 8);
+                        const float4 a0 = ps[0], a1 = ps[1], b0 = ph[0], b1 = ph[1];
+                        scs[0] = a0.x; scs[1] = a0.y; scs[2] = a0.z; scs[3] = a0.w; scs[4] = a1.x; scs[5] = a1.y; scs[6] = a1.z; scs[7] = a1.w;
+                        shs[0] = b0.x; shs[1] = b0.y; shs[2] = b0.z; shs[3] = b0.w; shs[4] = b1.x; shs[5] = b1.y; shs[6] = b1.z; shs[7] = b1.w;
+                    }
+                    const long long tq0 = p.dbg_out ? clock64() : 0;
+                    mbar_wait(&full_bar[xstage], xphase);
+                    const long long tq1 = p.dbg_out ? clock64() : 0;
+                    x_wait += tq1 - tq0;
+                    uint8_t *base = smem_a + xstage * kStageBytes;
+#pragma unroll
+                    for (int b0 = 0; b0 < kIters; b0 += kBatch) {
+                        if (p.dbg & 64) break;
+                        // all loads of a batch first, then the arithmetic, then the stores (the loop is latency bound otherwise)
+                        uint4 v[kBatch];
+                        bool ok[kBatch];
+#pragma unroll
+                        for (int i = 0; i < kBatch; ++i) {
+                            const uint32_t m = meta[b0 + i];
+                            const int hx = (int)((m >> 16) & 15u), hy = (int)((m >> 20) & 31u);
+                            // outside the image TMA wrote zeros = the conv padding of the NORMALISED tensor: leave them
+                            ok[i] = m != 0xFFFFFFFFu && hx >= hx_lo && hx < hx_hi && hy >= hy_lo && hy < hy_hi;
+                            if (ok[i]) v[i] = *reinterpret_cast<const uint4 *>(base + (m & 0xFFFFu));
+                        }
+#pragma unroll
+                        for (int i = 0; i < kBatch; ++i) {
+                            if (!ok[i]) continue;
+                            uint32_t *w = reinterpret_cast<uint32_t *>(&v[i]);
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) {
+                                const float2 f = unpack2<DT>(w[k]);
+                                float y0 = fmaf(f.x, scs[2 * k], shs[2 * k]), y1 = fmaf(f.y, scs[2 * k + 1], shs[2 * k + 1]);
+                                y0 = y0 > 0.f ? y0 : y0 * slope;
+                                y1 = y1 > 0.f ? y1 : y1 * slope;
+                                w[k] = pack2<DT>(y0, y1);
+                            }
+                        }
+#pragma unroll
+                        for (int i = 0; i < kBatch; ++i)
+                            if (ok[i]) *reinterpret_cast<uint4 *>(base + (meta[b0 + i] & 0xFFFFu)) = v[i];
+                    }
+                    if (!(p.dbg & 32)) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic-proxy writes -> visible to the MMA (async proxy)
+                    mbar_arrive(&ready_bar[xstage]);
+                    if (p.dbg_out) x_work += clock64() - tq1;
+                    if (++xstage == p.n_stages) { xstage = 0; xphase ^= 1; }
+                }
+                if (++xtx == p.tiles_x) { xtx = 0; if (++xty == p.tiles_y) { xty = 0; ++xn; } }
+            }
+            // ---------------- epilogue of local tile e = j - kLag ----------------
+            const int e = j - kLag;
+            if (e < 0 || !(kSplit || (e & 1) == grp)) continue;
+            const int buf = e & 1;
+            const uint32_t par = (uint32_t)(e >> 1) & 1u;
             const int x = tx * 8 + ix, y = ty * 16 + iy;
             const bool valid = (x < p.W) && (y < p.H) && !(p.dbg & 2);
             if (do_stats && n != cur_n) {
@@ -252,79 +352,36 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             mbar_arrive(&tmem_empty[buf]);        // this thread's TMEM reads of the tile are done
             uint32_t pk[16];
 #pragma unroll
-            for (int j = 0; j < 16; ++j) pk[j] = pack2<DT>(__uint_as_float(r[2 * j]) + bias_r[2 * j], __uint_as_float(r[2 * j + 1]) + bias_r[2 * j + 1]);
+            for (int k = 0; k < 8; ++k) {
+                const float4 b = *reinterpret_cast<const float4 *>(&s_bias[col0 + 4 * k]);     // warp-uniform address: broadcast
+                pk[2 * k] = pack2<DT>(__uint_as_float(r[4 * k]) + b.x, __uint_as_float(r[4 * k + 1]) + b.y);
+                pk[2 * k + 1] = pack2<DT>(__uint_as_float(r[4 * k + 2]) + b.z, __uint_as_float(r[4 * k + 3]) + b.w);
+            }
             if (valid) {
                 // 2 x 32-byte stores (STG.256): every sector is written whole by one instruction
 #pragma unroll
-                for (int j = 0; j < 2; ++j)
-                    asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst + 16 * j), "r"(pk[8 * j]), "r"(pk[8 * j + 1]),
-                                 "r"(pk[8 * j + 2]), "r"(pk[8 * j + 3]), "r"(pk[8 * j + 4]), "r"(pk[8 * j + 5]), "r"(pk[8 * j + 6]), "r"(pk[8 * j + 7]) : "memory");
+                for (int k = 0; k < 2; ++k)
+                    asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst + 16 * k), "r"(pk[8 * k]), "r"(pk[8 * k + 1]),
+                                 "r"(pk[8 * k + 2]), "r"(pk[8 * k + 3]), "r"(pk[8 * k + 4]), "r"(pk[8 * k + 5]), "r"(pk[8 * k + 6]), "r"(pk[8 * k + 7]) : "memory");
                 if (do_stats) {
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        const float2 f = unpack2<DT>(pk[j]);          // statistics of the ROUNDED values (what the consumer normalises)
-                        tacc1[2 * j] += f.x;
-                        tacc1[2 * j + 1] += f.y;
-                        tacc2[2 * j] = fmaf(f.x, f.x, tacc2[2 * j]);
-                        tacc2[2 * j + 1] = fmaf(f.y, f.y, tacc2[2 * j + 1]);
+                    for (int k = 0; k < 16; ++k) {
+                        const float2 f = unpack2<DT>(pk[k]);          // statistics of the ROUNDED values (what the consumer normalises)
+                        tacc1[2 * k] += f.x;
+                        tacc1[2 * k + 1] += f.y;
+                        tacc2[2 * k] = fmaf(f.x, f.x, tacc2[2 * k]);
+                        tacc2[2 * k + 1] = fmaf(f.y, f.y, tacc2[2 * k + 1]);
                     }
                 }
             }
-            tx += sx; if (tx >= p.tiles_x) { tx -= p.tiles_x; ++ty; }
-            ty += sy; if (ty >= p.tiles_y) { ty -= p.tiles_y; ++n; }
-            n += sn;
+            tx += esx; if (tx >= p.tiles_x) { tx -= p.tiles_x; ++ty; }
+            ty += esy; if (ty >= p.tiles_y) { ty -= p.tiles_y; ++n; }
+            n += esn;
         }
         if (do_stats && cur_n >= 0) flush_stats(cur_n);
-        if (p.dbg_out && threadIdx.x == 64) p.dbg_out[(size_t)(blockIdx.y * gridDim.x + blockIdx.x) * 4 + 3] = (unsigned long long)w_epi;
-    } else if (FUSE) {
-        // ===================== halo transform (warps 6..9): producer's InstanceNorm-apply + LeakyReLU =====================
-        // thread t handles 16-byte chunks (8 channels) of the halo: chunk g -> pixel g / (KC/8), channel block g % (KC/8)
-        const int t = threadIdx.x - 320;
-        constexpr int kChunksPerPix = KC / 8;                 // 16-byte chunks (8 channels) per halo pixel
-        constexpr int kPixStep = 128 / kChunksPerPix;         // 128 % kChunksPerPix == 0: a thread keeps ONE channel block
-        constexpr uint32_t kXorMask = (KC == 64) ? 7u : 3u;
-        const int cb = t % kChunksPerPix, pix0 = t / kChunksPerPix;
-        float scs[8], shs[8], sls[8];
-        int cur_n = -1, cur_cc = -1;
-        int stage = 0;
-        uint32_t phase = 0;
-        for (int tile = t_begin; tile < t_end; ++tile) {
-            const int tx = tile % p.tiles_x, ty = (tile / p.tiles_x) % p.tiles_y, n = tile / tiles_per_img + p.n_base;
-            for (int cc = 0; cc < p.cin_chunks; ++cc) {
-                if (n != cur_n || cc != cur_cc) {
-                    const long long o = (long long)n * p.Cin + cc * KC + cb * 8;
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) { scs[j] = __ldg(p.in_scale + o + j); shs[j] = __ldg(p.in_shift + o + j); sls[j] = __ldg(p.in_slope + cc * KC + cb * 8 + j); }
-                    cur_n = n; cur_cc = cc;
-                }
-                mbar_wait(&full_bar[stage], phase);
-                uint8_t *base = smem_a + stage * kStageBytes;
-                const uint32_t base_u32 = smem_u32(base);
-                for (int pix = pix0; pix < kHaloPix; pix += kPixStep) {
-                    const int hx = pix % kHaloW, hy = pix / kHaloW;
-                    const int gx = tx * 8 - 1 + hx, gy = ty * 16 - 1 + hy;
-                    // outside the image TMA wrote zeros = the conv padding of the NORMALISED tensor: leave them
-                    if (gx < 0 || gx >= p.W || gy < 0 || gy >= p.H) continue;
-                    // absolute-address swizzle: 16-byte chunk index XOR ((byte address >> 7) & mask)
-                    const uint32_t row_off = (uint32_t)(pix * kRowB);
-                    const uint32_t sw = ((base_u32 + row_off) >> 7) & kXorMask;
-                    uint4 *ptr = reinterpret_cast<uint4 *>(base + row_off + (((uint32_t)cb ^ sw) << 4));
-                    uint4 v = *ptr;
-                    uint32_t *w = reinterpret_cast<uint32_t *>(&v);
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const float2 f = unpack2<DT>(w[j]);
-                        float y0 = fmaf(f.x, scs[2 * j], shs[2 * j]), y1 = fmaf(f.y, scs[2 * j + 1], shs[2 * j + 1]);
-                        y0 = fmaxf(y0, y0 * sls[2 * j]);              // LeakyReLU for 0 <= slope <= 1 (slope 1 = identity)
-                        y1 = fmaxf(y1, y1 * sls[2 * j + 1]);
-                        w[j] = pack2<DT>(y0, y1);
-                    }
-                    *ptr = v;
-                }
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic-proxy writes -> visible to the MMA (async proxy)
-                mbar_arrive(&ready_bar[stage]);
-                if (++stage == p.n_stages) { stage = 0; phase ^= 1; }
-            }
+        if (p.dbg_out && wt == 0) {
+            unsigned long long *o = p.dbg_out + (size_t)(blockIdx.y * gridDim.x + blockIdx.x) * 8;
+            o[3] = (unsigned long long)w_epi; o[4] = (unsigned long long)x_wait; o[5] = (unsigned long long)x_work;
         }
     }
     tcgen05_fence_before();

@@ -62,6 +62,10 @@ struct ConvLayer {
     int halo_bn = 0, halo_stages = 0;
     bool halo_maps = false;
     bool first_fast = false;    // conv_first_kernel (CIN <= 4, 3x3 stride 1, 16-bit activations)
+    void *out_raw = nullptr;    // pre-normalisation output (ping-pong between two buffers)
+    bool defer = false;         // no norm_act pass: the consumer applies InstanceNorm + LeakyReLU on its operand path
+    int prod = -1;              // >= 0: the input is conv `prod`'s raw output (this layer runs conv_halo_kernel<FUSE>)
+    bool materialized = false;  // per forward: norm_out holds the normalised tensor
 };
 
 struct UpLayer {
@@ -98,7 +102,8 @@ struct ts2d_unet {
     uint8_t *arena = nullptr;
     size_t arena_bytes = 0;
     std::vector<void *> cat;
-    void *bott = nullptr, *raw = nullptr, *tmpA = nullptr, *tmpB = nullptr;
+    void *bott = nullptr, *raw = nullptr, *rawB = nullptr, *tmpA = nullptr, *tmpB = nullptr;
+    float *feat_ss = nullptr;     // [N][C0][2] scale / shift of the last decoder conv when its norm is deferred to the blend kernel
     double *stats_arena = nullptr;
     size_t stats_bytes = 0;
     void *features = nullptr;     // last decoder output [N][P][P][C0]
@@ -207,7 +212,8 @@ constexpr int kHaloSmemBudget = 225 * 1024;
 static int halo_smem_bytes(int cin, int bn, int kc, int stages) {
     const int w = ((9 * cin * bn * 2) + 1023) & ~1023;
     const int st = kc == 64 ? halo_stage_bytes<64>() : halo_stage_bytes<32>();
-    return 1024 /*align*/ + w + stages * st + 512 /*barriers*/ + bn * 4 + 64;
+    (void)bn;
+    return 1024 /*align*/ + w + stages * st + kHaloTailBytes;
 }
 template <int BN, int KC, typename DT, bool FUSE>
 static int launch_halo_inst(const CUtensorMap &tmA, const CUtensorMap &tmB, const ConvHaloParams &p, int smem, cudaStream_t st) {
@@ -219,7 +225,7 @@ static int launch_halo_inst(const CUtensorMap &tmA, const CUtensorMap &tmB, cons
     const int n_tiles_n = p.Cout / BN;
     const int total = p.tiles_x * p.tiles_y * p.N;
     const int gx = std::max(1, std::min(total, kNumSMs / n_tiles_n));
-    conv_halo_kernel<BN, KC, DT, FUSE><<<dim3(gx, n_tiles_n), FUSE ? 448 : 320, smem, st>>>(tmA, tmB, p);
+    conv_halo_kernel<BN, KC, DT, FUSE><<<dim3(gx, n_tiles_n), kHaloThreads, smem, st>>>(tmA, tmB, p);
     TS2D_LAUNCH_CHECK();
     return TS2D_OK;
 }
@@ -505,6 +511,8 @@ extern "C" int ts2d_unet_finalize(ts2d_unet *u) {
     size_t max_act = 0;
     for (auto &c : u->convs) max_act = std::max(max_act, (size_t)N * c.Hout * c.Wout * c.cout * es);
     const size_t raw_off = off; off += align(max_act);
+    const size_t rawb_off = off; off += align(max_act);
+    const size_t ss_off = off; off += align((size_t)N * u->C[0] * 2 * sizeof(float));
     const size_t a_off = off; off += align(max_act);
     const size_t b_off = off; off += align(max_act);
     const size_t stats_off = off;
@@ -517,7 +525,8 @@ extern "C" int ts2d_unet_finalize(ts2d_unet *u) {
     u->arena_bytes = off;
     u->cat.resize(L - 1);
     for (int l = 0; l < L - 1; ++l) u->cat[l] = u->arena + cat_off[l];
-    u->bott = u->arena + bott_off; u->raw = u->arena + raw_off; u->tmpA = u->arena + a_off; u->tmpB = u->arena + b_off;
+    u->bott = u->arena + bott_off; u->raw = u->arena + raw_off; u->rawB = u->arena + rawb_off;
+    u->feat_ss = reinterpret_cast<float *>(u->arena + ss_off); u->tmpA = u->arena + a_off; u->tmpB = u->arena + b_off;
     u->stats_arena = reinterpret_cast<double *>(u->arena + stats_off);
     u->stats_bytes = sbytes;
     size_t so = 0;
@@ -566,6 +575,31 @@ extern "C" int ts2d_unet_finalize(ts2d_unet *u) {
         c.halo = halo_config(c, c.halo_bn, c.halo_stages);
         c.halo_maps = false;
         c.first_fast = !c.tc && first_fast_eligible(pl, c);
+        c.defer = false; c.prod = -1;
+    }
+    // ---- deferred normalisation: producer writes raw + statistics only, the consumer normalises while loading ----
+    // TS2D_FUSE_NORM: 0 = every layer runs norm_act_kernel; 1 (default) = the last decoder conv is normalised inside the blend
+    // kernel; 2 = additionally conv_halo_kernel<FUSE> consumers (correct and bit-identical, but measured slower than the
+    // HBM-bound norm pass it replaces: the in-smem transform costs as many issue slots as the epilogue, see profiles/)
+    {
+        const int fuse = getenv("TS2D_FUSE_NORM") ? atoi(getenv("TS2D_FUSE_NORM")) : 1;
+        for (size_t i = 0; i < u->convs.size(); ++i) u->convs[i].out_raw = (i & 1) ? u->rawB : u->raw;
+        size_t k = 0;
+        auto stage_pass = [&](int n_convs) {
+            for (int i = 0; i + 1 < n_convs; ++i) {
+                ConvLayer &prod = u->convs[k + i], &cons = u->convs[k + i + 1];
+                // the fused kernel's workers run the epilogue of tile j-2 after the transform of tile j: the ring must hold a whole tile
+                if (fuse >= 2 && cons.halo && pl.precision != TS2D_PREC_F32 && cons.halo_stages >= cons.cin / cons.kc && cons.cin <= 256) {
+                    prod.defer = true;
+                    cons.prod = (int)(k + i);
+                    cons.in = prod.out_raw; cons.in_ps = prod.cout;
+                }
+            }
+            k += n_convs;
+        };
+        for (int s = 0; s < L; ++s) stage_pass(pl.n_conv_enc[s]);
+        for (int d = 0; d < L - 1; ++d) stage_pass(pl.n_conv_dec[d]);
+        u->convs.back().defer = fuse != 0;      // the blend kernel applies the last InstanceNorm + LeakyReLU
     }
     for (auto &up : u->ups) {
         up.tc = tc_eligible(pl, up.cin, up.cout, 1, 1, 1, 1, up.Hin, up.Win, up.cin);
@@ -614,6 +648,8 @@ static int prof_end(ts2d_unet *u, const std::string &name, int kind, double flop
     return TS2D_OK;
 }
 
+static int run_norm(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st);
+
 static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
     const ts2d_unet_plan &pl = u->plan;
     const size_t es = u->es;
@@ -627,16 +663,22 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
         p.cin_chunks = c.cin / c.kc;
         p.tiles_x = ceil_div(c.Wout, 8); p.tiles_y = ceil_div(c.Hout, 16);
         p.n_stages = c.halo_stages;
-        p.out_ps = c.cout; p.out = u->raw; p.bias = c.b.dev; p.stats = c.stats;
+        p.out_ps = c.cout; p.out = c.out_raw; p.bias = c.b.dev; p.stats = c.stats;
         p.Cin = c.cin;
+        const bool fuse = c.prod >= 0;
+        if (fuse) {
+            const ConvLayer &pr = u->convs[c.prod];
+            p.in_stats = pr.stats; p.in_gamma = pr.gamma.dev; p.in_beta = pr.beta.dev; p.in_hw = pr.Hout * pr.Wout;
+            p.in_eps = pl.eps; p.in_slope = pl.negative_slope;
+        }
         if (c.first || !c.halo_maps) {
             if ((rc = encode_act_map(&c.tmA, c.in, c.in_ps, c.cin, c.Hin, c.Win, pl.max_batch, false, c.kc, kHaloW, kHaloH, 1, es, is_bf16))) return rc;
             if ((rc = encode_w_map(&c.tmB, c.w_tc, c.cin, c.cout, 9, c.kc, c.halo_bn, es, is_bf16))) return rc;
             c.halo_maps = true;
         }
         const int smem = halo_smem_bytes(c.cin, c.halo_bn, c.kc, c.halo_stages);
-        rc = is_bf16 ? launch_halo<__nv_bfloat16>(c.halo_bn, c.kc, false, c.tmA, c.tmB, p, smem, st)
-                     : launch_halo<__half>(c.halo_bn, c.kc, false, c.tmA, c.tmB, p, smem, st);
+        rc = is_bf16 ? launch_halo<__nv_bfloat16>(c.halo_bn, c.kc, fuse, c.tmA, c.tmB, p, smem, st)
+                     : launch_halo<__half>(c.halo_bn, c.kc, fuse, c.tmA, c.tmB, p, smem, st);
         if (rc) return rc;
     } else if (c.tc) {
         ConvTcParams p;
@@ -648,7 +690,7 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
         fill_tc_params(p, N, c.Hout, c.Wout, c.cout, c.cin, c.kc, bn, c.kh * c.kw, c.kw, (c.kh - 1) / 2, (c.kw - 1) / 2, s2, c.in_ps);
         p.tw = tw; p.th = th; p.tn = tn;
         p.tiles_w = ceil_div(c.Wout, tw); p.tiles_h = ceil_div(c.Hout, th); p.tiles_n = ceil_div(N, tn);
-        p.out_ps = c.cout; p.out = u->raw; p.bias = c.b.dev; p.stats = c.stats;
+        p.out_ps = c.cout; p.out = c.out_raw; p.bias = c.b.dev; p.stats = c.stats;
         // descriptors depend on (input pointer, batch-dependent tile box, BN): cache by (N, bn)
         if (c.first || c.bn != bn || c.enc_n != N) {
             if ((rc = encode_act_map(&c.tmA, c.in, c.in_ps, c.cin, c.Hin, c.Win, pl.max_batch, s2, c.kc, tw, th, tn, es, is_bf16))) return rc;
@@ -661,7 +703,7 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
     } else if (c.first_fast) {
         FirstConvParams p;
         memset(&p, 0, sizeof(p));
-        p.in = c.in; p.H = c.Hin; p.W = c.Win; p.w = c.w_direct; p.bias = c.b.dev; p.out = u->raw; p.Cout = c.cout; p.stats = c.stats;
+        p.in = c.in; p.H = c.Hin; p.W = c.Win; p.w = c.w_direct; p.bias = c.b.dev; p.out = c.out_raw; p.Cout = c.cout; p.stats = c.stats;
         rc = is_bf16 ? launch_first<__nv_bfloat16>(c.cin, p, N, st) : launch_first<__half>(c.cin, p, N, st);
         if (rc) return rc;
     } else {
@@ -669,7 +711,7 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
         memset(&p, 0, sizeof(p));
         p.in = c.in; p.in_ps = c.in_ps; p.Hin = c.Hin; p.Win = c.Win; p.Cin = c.cin;
         p.w = c.w_direct; p.bias = c.b.dev;
-        p.out = u->raw; p.out_ps = c.cout; p.Hout = c.Hout; p.Wout = c.Wout; p.Cout = c.cout;
+        p.out = c.out_raw; p.out_ps = c.cout; p.Hout = c.Hout; p.Wout = c.Wout; p.Cout = c.cout;
         p.kh = c.kh; p.kw = c.kw; p.sh = c.sh; p.sw = c.sw; p.ph = (c.kh - 1) / 2; p.pw = (c.kw - 1) / 2;
         p.my = 1; p.mx = 1; p.dy = 0; p.dx = 0; p.Hfull = c.Hout; p.Wfull = c.Wout;
         p.stats = c.stats;
@@ -681,11 +723,22 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
         if ((rc = prof_end(u, c.name, 0, 2.0 * px * c.kh * c.kw * c.cin * c.cout,
                            ((double)N * c.Hin * c.Win * c.cin + px * c.cout) * es, st))) return rc;
     }
+    c.materialized = false;
+    if (c.defer) return TS2D_OK;
+    return run_norm(u, c, N, st);
+}
+
+// InstanceNorm-apply + LeakyReLU of conv `c` into its norm_out (skipped for deferred layers unless someone needs the tensor)
+static int run_norm(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
+    const ts2d_unet_plan &pl = u->plan;
+    const size_t es = u->es;
+    int rc;
     if ((rc = prof_begin(u, st))) return rc;
-    rc = launch_norm_any(pl.precision, u->raw, c.stats, c.gamma.dev, c.beta.dev, c.norm_out, c.out_ps, c.Hout * c.Wout, c.cout, pl.eps,
+    rc = launch_norm_any(pl.precision, c.out_raw, c.stats, c.gamma.dev, c.beta.dev, c.norm_out, c.out_ps, c.Hout * c.Wout, c.cout, pl.eps,
                          pl.negative_slope, N, st);
     if (rc) return rc;
     u->launches++;
+    c.materialized = true;
     if ((rc = prof_end(u, c.name + ".norm", 2, 0.0, 2.0 * N * c.Hout * c.Wout * c.cout * es, st))) return rc;
     return TS2D_OK;
 }
@@ -754,6 +807,7 @@ static int forward_impl(ts2d_unet *u, const void *x, int batch, const char *stop
             ConvLayer &c = u->convs[op.idx];
             if ((rc = run_conv(u, c, batch, st))) return rc;
             if (stop_layer && c.name == stop_layer) {
+                if (!c.materialized && (rc = run_norm(u, c, batch, st))) return rc;
                 const int HW = c.Hout * c.Wout;
                 dim3 grid(std::min(ceil_div((long long)HW * c.cout, 256), kNumSMs * 8), batch);
                 if (u->plan.precision == TS2D_PREC_F32) nhwc_to_nchw_f32_kernel<float><<<grid, 256, 0, st>>>((const float *)c.norm_out, c.out_ps, c.cout, HW, debug_out);
@@ -801,6 +855,10 @@ extern "C" int ts2d_unet_tile_logits(ts2d_unet *u, int batch, float *logits_dev,
     const int HW = u->plan.patch_h * u->plan.patch_w, F = u->C[0], heads = u->plan.num_heads;
     dim3 grid(ceil_div(HW, 128), batch);
     cudaStream_t st = (cudaStream_t)stream;
+    if (!u->convs.back().materialized) {
+        int rc = run_norm(u, u->convs.back(), u->last_batch, st);
+        if (rc) return rc;
+    }
     if (u->plan.precision == TS2D_PREC_F32) tile_logits_kernel<float><<<grid, 128, 0, st>>>((const float *)u->features, F, u->head_w.dev, u->head_b.dev, heads, HW, logits_dev);
     else if (u->plan.precision == TS2D_PREC_BF16) tile_logits_kernel<__nv_bfloat16><<<grid, 128, 0, st>>>((const __nv_bfloat16 *)u->features, F, u->head_w.dev, u->head_b.dev, heads, HW, logits_dev);
     else tile_logits_kernel<__half><<<grid, 128, 0, st>>>((const __half *)u->features, F, u->head_w.dev, u->head_b.dev, heads, HW, logits_dev);
@@ -851,6 +909,16 @@ extern "C" int ts2d_unet_blend_head(ts2d_unet *u, const int *tile_yx_host, int T
     p.present = present_dev;
     cudaStream_t st = (cudaStream_t)stream;
     int rc;
+    ConvLayer &lastc = u->convs.back();
+    if (!lastc.materialized) {
+        // the last decoder conv left raw output + statistics: finalise {scale, shift} per (image, channel), normalise inside the blend
+        const int NC = u->last_batch * lastc.cout;
+        norm_finalize_kernel<<<ceil_div(NC, 256), 256, 0, st>>>(lastc.stats, lastc.gamma.dev, lastc.beta.dev, u->feat_ss, NC, lastc.cout,
+                                                                 lastc.Hout * lastc.Wout, u->plan.eps);
+        TS2D_LAUNCH_CHECK();
+        u->launches++;
+        p.feat = lastc.out_raw; p.feat_ss = u->feat_ss; p.slope = u->plan.negative_slope;
+    }
     if (u->plan.precision == TS2D_PREC_F32) rc = launch_blend_any<float>(p, tile_yx_host, u->C[0], st);
     else if (u->plan.precision == TS2D_PREC_BF16) rc = launch_blend_any<__nv_bfloat16>(p, tile_yx_host, u->C[0], st);
     else rc = launch_blend_any<__half>(p, tile_yx_host, u->C[0], st);

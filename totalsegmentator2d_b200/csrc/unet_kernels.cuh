@@ -247,6 +247,21 @@ __global__ void __launch_bounds__(256) norm_act_kernel(const T *raw, const doubl
     }
 }
 
+// scale / shift of InstanceNorm per (image, channel) from the epilogue statistics: ss[(n*C + c)*2] = {scale, shift};
+// same arithmetic as norm_act_kernel.  Used when the last decoder conv's normalisation is applied by blend_head_kernel.
+__global__ void __launch_bounds__(256) norm_finalize_kernel(const double *stats, const float *gamma, const float *beta, float *ss, int NC, int C,
+                                                            int HW, float eps) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= NC) return;
+    const int c = i % C;
+    const double mean = stats[(long long)i * 2] / (double)HW;
+    const double var = fmax(stats[(long long)i * 2 + 1] / (double)HW - mean * mean, 0.0);
+    const double rstd = 1.0 / sqrt(var + (double)eps);
+    const float g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
+    ss[(long long)i * 2] = (float)(rstd * (double)g);
+    ss[(long long)i * 2 + 1] = (float)((double)b - mean * rstd * (double)g);
+}
+
 // ------------------------------------------------------------------------------------------------------
 // Fused: mirror-TTA average + Gaussian-weighted tile blend + 1x1 segmentation head + (logits | threshold+paste).
 // The head is linear, so  sum_t g_t (W f_t + b) / sum_t g_t  ==  W (sum_t g_t f_t / sum_t g_t) + b : the F-channel
@@ -264,6 +279,8 @@ struct BlendParams {
     uint8_t *mask;             // [H0][W0][ch_total] or null
     int W0, h0, w0, ch_off, ch_total;
     uint8_t *present;          // [ch_total] or null
+    const float *feat_ss;      // null: feat is normalised + activated; else feat is the raw conv output and {scale, shift}
+    float slope;               //       [T*M][F][2] + LeakyReLU(slope) are applied here (rounded to T like norm_act_kernel does)
 };
 
 template <typename T, int F, int CAP>
@@ -295,7 +312,16 @@ __global__ void __launch_bounds__(128) blend_head_kernel(const BlendParams p, co
             else if (p.mirror_mask == 2) fw = (m == 1);
             const int sy = fh ? p.Ph - 1 - ly : ly, sx = fw ? p.Pw - 1 - lx : lx;
             const T *f = feat + (((long long)(t * p.M + m) * p.Ph + sy) * p.Pw + sx) * F;
-            if constexpr (sizeof(T) == 2 && (F % 8) == 0) {
+            if (p.feat_ss) {
+                const float2 *ss = reinterpret_cast<const float2 *>(p.feat_ss) + (long long)(t * p.M + m) * F;     // warp-uniform: broadcast loads
+#pragma unroll
+                for (int k = 0; k < F; ++k) {
+                    const float2 c = __ldg(ss + k);
+                    float y = fmaf(to_f32<T>(f[k]), c.x, c.y);
+                    y = y > 0.f ? y : y * p.slope;
+                    acc[k] = fmaf(gm, to_f32<T>(from_f32<T>(y)), acc[k]);
+                }
+            } else if constexpr (sizeof(T) == 2 && (F % 8) == 0) {
 #pragma unroll
                 for (int k = 0; k < F; k += 8) {
                     uint4 v = *reinterpret_cast<const uint4 *>(f + k);
