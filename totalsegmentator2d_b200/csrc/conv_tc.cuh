@@ -14,12 +14,16 @@
 //   B  weights repacked [tap][Cout][Cin] (K-major), 3-D TMA box (KC, BN, 1).
 //   D  fp32 accumulators in TMEM, double buffered (2 x BN columns): the epilogue of tile i overlaps the MMAs
 //      of tile i+1.
-// Warp roles (192 threads): warp 0 = TMA producer (one lane), warp 1 = TMEM allocator + MMA issuer (one lane),
-// warps 2-5 = epilogue (TMEM lane group = warp % 4): tcgen05.ld -> +bias -> round to bf16/fp16 -> per-channel
-// sum / sum-of-squares of the ROUNDED values for InstanceNorm (warp transpose-reduction, accumulated in registers
-// across the CTA's tiles, flushed with double atomics when the image index changes) -> 16-byte global stores.
-// Persistent grid: one CTA per SM, static round-robin over (m_tile, n_tile) with n fastest so that CTAs running
-// concurrently share the A tile through L2.
+// Transposed conv (kernel == stride): a 1x1 GEMM whose N axis is (tap, Cout): all taps of a pixel come out of ONE pass
+// over A; the epilogue scatters column block (tap, c0) to output pixel (y*my + tap/mx, x*mx + tap%mx).
+// Warp roles (384 threads): warp 0 = TMA producer (one lane), warp 1 = TMEM allocator + MMA issuer (whole warp
+// convergent, one elected lane issues), warps 2-3 idle, warps 4-11 = epilogue, two warpgroups (TMEM lane quarter =
+// warp % 4): tcgen05.ld -> +bias -> round to bf16/fp16 -> InstanceNorm sum / sum-of-squares of the ROUNDED values ->
+// 32-byte global stores.  BN == 32: the groups alternate tiles; BN >= 64: each group takes half of the tile's columns.
+// Statistics: per-thread running sums (BN <= 64) or per-tile warp transpose-reductions into per-lane sums (BN >= 128),
+// flushed with double atomics when the (image, channel block) of the CTA's tile sequence changes.
+// Persistent grid: one CTA per SM, static CONTIGUOUS partition of the tile sequence (channel block slowest, then image,
+// y, x): a CTA touches few images (few flushes, spread in time) and neighbouring CTAs share weights through L2.
 #pragma once
 #include "common.cuh"
 
@@ -35,14 +39,15 @@ struct ConvTcParams {
     int tw, th, tn;              // tile box: tw*th*tn == 128
     int tiles_w, tiles_h, tiles_n;
     int n_tiles_n;               // Cout / BN
+    int tap_cout;                // transposed conv: output channels per tap (Cout = taps_out * tap_cout); else == Cout
     // output addressing: pixel (n, y*my + dy, x*mx + dx) of an image Hfull x Wfull with pixel stride out_ps elements
     int my, mx, Hfull, Wfull;
     long long out_ps;
     void *out;
     const float *bias;           // [Cout] or null
     double *stats;               // [N][Cout][2] or null
-    int tap_base_from_grid_y;    // transposed conv: blockIdx.y selects (dy,dx) = weight slice and output offset
 };
+constexpr int kTcThreads = 384;
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -198,13 +203,17 @@ __device__ __forceinline__ float warp_transpose_sum32(float (&x)[32], int lane) 
     return x[0];
 }
 
+
 template <int BN, int KC, typename DT>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(kTcThreads, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const ConvTcParams p) {
     constexpr int kStages = tc_num_stages<BN, KC>();
     constexpr int kABytes = 128 * KC * 2;
     constexpr int kStageBytes = tc_stage_bytes<BN, KC>();
     constexpr int kTmemCols = TcCfg<BN>::kTmemCols;
+    constexpr bool kAlt = BN == 32;                          // epilogue groups alternate tiles (else: split the columns)
+    constexpr int kMyChunks = kAlt ? 1 : BN / 64;            // 32-column chunks per epilogue thread and tile
+    constexpr bool kThreadAcc = kMyChunks == 1;              // per-thread statistics accumulators (64 registers)
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -216,13 +225,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    const int tap_base = p.tap_base_from_grid_y ? blockIdx.y : 0;
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
         for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-        for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], 128); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], kAlt ? 128 : 256); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -237,14 +245,17 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int m_tiles = p.tiles_n * p.tiles_h * p.tiles_w;
     const int total_tiles = m_tiles * p.n_tiles_n;
     const int k_chunks = p.taps * p.cin_chunks;
+    // tile t -> channel block nt = t / m_tiles (slowest), m tile = t % m_tiles = (image group, y tile, x tile) with x fastest
+    const int t_begin = (int)((long long)total_tiles * blockIdx.x / gridDim.x);
+    const int t_end = (int)((long long)total_tiles * (blockIdx.x + 1) / gridDim.x);
 
     if (warp == 0) {
         // ===================== TMA producer =====================
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-                const int mt = tile / p.n_tiles_n, nt = tile % p.n_tiles_n;
+            for (int tile = t_begin; tile < t_end; ++tile) {
+                const int nt = tile / m_tiles, mt = tile - nt * m_tiles;
                 const int xt = mt % p.tiles_w, yt = (mt / p.tiles_w) % p.tiles_h, nn = mt / (p.tiles_w * p.tiles_h);
                 const int x0 = xt * p.tw, y0 = yt * p.th, n0 = nn * p.tn;
                 for (int kc = 0; kc < k_chunks; ++kc) {
@@ -263,7 +274,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         const int hoff = (dr - py) / 2, woff = (ds - px) / 2;
                         tma_load_5d(sa, &tmA, &full_bar[stage], px * p.in_ps + cc * KC, x0 + woff, py, y0 + hoff, n0);
                     }
-                    tma_load_3d(sb, &tmB, &full_bar[stage], cc * KC, nt * BN, tap_base + tap);
+                    tma_load_3d(sb, &tmB, &full_bar[stage], cc * KC, nt * BN, tap);
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
             }
@@ -277,7 +288,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         int stage = 0;
         uint32_t phase = 0;
         int it = 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+        for (int tile = t_begin; tile < t_end; ++tile, ++it) {
             const int buf = it & 1;
             const uint32_t use = (uint32_t)(it >> 1);
             mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);
@@ -296,98 +307,140 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
             tcgen05_commit_pred(leader, &tmem_full[buf]);             // accumulator complete
         }
-    } else {
-        // ===================== epilogue (warps 2..5) =====================
-        const int q = warp & 3;                 // TMEM lane group this warp may access
+    } else if (warp >= 4) {
+        // ===================== epilogue (warps 4..11, two warpgroups) =====================
+        const int grp = (warp - 4) >> 2;
+        const int q = warp & 3;                 // TMEM lane quarter this warp may access
         const int row = q * 32 + lane;          // accumulator row = pixel index in the tile
         const int ix = row % p.tw, iy = (row / p.tw) % p.th, in_ = row / (p.tw * p.th);
+        const int chunk0 = kAlt ? 0 : grp * kMyChunks;
         DT *out = reinterpret_cast<DT *>(p.out);
         const bool do_stats = p.stats != nullptr;
-        const bool fast_stats = do_stats && p.tn == 1;
-        float racc1[BN / 32], racc2[BN / 32];
+        const bool fast_stats = do_stats && p.tn == 1;     // a tile lies inside one image: sums can stay in registers across tiles
+        float tacc1[kThreadAcc ? 32 : 1], tacc2[kThreadAcc ? 32 : 1];     // per-thread sums of this thread's pixel row (kThreadAcc)
+        float racc1[kMyChunks], racc2[kMyChunks];                         // per-lane (= per-channel) sums (otherwise)
 #pragma unroll
-        for (int i = 0; i < BN / 32; ++i) { racc1[i] = 0.f; racc2[i] = 0.f; }
+        for (int i = 0; i < (kThreadAcc ? 32 : 1); ++i) { tacc1[i] = 0.f; tacc2[i] = 0.f; }
+#pragma unroll
+        for (int i = 0; i < kMyChunks; ++i) { racc1[i] = 0.f; racc2[i] = 0.f; }
+        auto flush_stats = [&](int n_img, int nt_blk) {
+            if constexpr (kThreadAcc) {
+                float b[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) b[j] = tacc2[j];
+                racc1[0] = warp_transpose_sum32(tacc1, lane);
+                racc2[0] = warp_transpose_sum32(b, lane);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) { tacc1[j] = 0.f; tacc2[j] = 0.f; }
+            }
+#pragma unroll
+            for (int c = 0; c < kMyChunks; ++c) {
+                double *s = p.stats + ((long long)n_img * p.Cout + nt_blk * BN + (chunk0 + c) * 32 + lane) * 2;
+                atomicAdd(s, (double)racc1[c]);
+                atomicAdd(s + 1, (double)racc2[c]);
+                racc1[c] = 0.f; racc2[c] = 0.f;
+            }
+        };
         int cur_n = -1, cur_nt = -1;
-        int it = 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-            const int mt = tile / p.n_tiles_n, nt = tile % p.n_tiles_n;
-            const int xt = mt % p.tiles_w, yt = (mt / p.tiles_w) % p.tiles_h, nn = mt / (p.tiles_w * p.tiles_h);
+        // tile walker (no divisions in the loop): this group's tiles are t_begin + e, e += estep
+        const int estep = kAlt ? 2 : 1;
+        int tile = t_begin + (kAlt ? grp : 0);
+        int nt = tile / m_tiles;
+        int xt, yt, nn;
+        {
+            const int mt = tile - nt * m_tiles;
+            xt = mt % p.tiles_w; yt = (mt / p.tiles_w) % p.tiles_h; nn = mt / (p.tiles_w * p.tiles_h);
+        }
+        for (int e = kAlt ? grp : 0; tile < t_end; tile += estep, e += estep) {
+            const int buf = e & 1;
+            const uint32_t par = (uint32_t)(e >> 1) & 1u;
             const int x = xt * p.tw + ix, y = yt * p.th + iy, n = nn * p.tn + in_;
             const bool valid = (x < p.Wout) && (y < p.Hout) && (n < p.N);
-            if (fast_stats && (n != cur_n || nt != cur_nt)) {
-                if (cur_n >= 0) {
-#pragma unroll
-                    for (int i = 0; i < BN / 32; ++i) {
-                        double *s = p.stats + ((long long)cur_n * p.Cout + cur_nt * BN + i * 32 + lane) * 2;
-                        atomicAdd(s, (double)racc1[i]);
-                        atomicAdd(s + 1, (double)racc2[i]);
-                        racc1[i] = 0.f; racc2[i] = 0.f;
-                    }
-                }
-                cur_n = nn * p.tn;   // tn == 1 -> the tile's image
+            if (fast_stats && (nn != cur_n || nt != cur_nt)) {
+                if (cur_n >= 0) flush_stats(cur_n, cur_nt);
+                cur_n = nn;          // tn == 1 -> the tile's image
                 cur_nt = nt;
             }
-            const int buf = it & 1;
-            const uint32_t use = (uint32_t)(it >> 1);
-            mbar_wait(&tmem_full[buf], use & 1);
+            mbar_wait(&tmem_full[buf], par);
             tcgen05_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BN);
-            int dy = 0, dx = 0;
-            if (p.tap_base_from_grid_y) { dy = blockIdx.y / p.mx; dx = blockIdx.y % p.mx; }
-            DT *orow = out + (((long long)n * p.Hfull + (long long)y * p.my + dy) * p.Wfull + (long long)x * p.mx + dx) * p.out_ps + nt * BN;
+            DT *opix = out + (((long long)n * p.Hfull + (long long)y * p.my) * p.Wfull + (long long)x * p.mx) * p.out_ps;
 #pragma unroll
-            for (int ch = 0; ch < BN / 32; ++ch) {
+            for (int c = 0; c < kMyChunks; ++c) {
+                const int chunk = chunk0 + c;
                 uint32_t r[32];
-                tmem_ld_32x32b_x32(taddr + ch * 32, r);
+                tmem_ld_32x32b_x32(taddr + chunk * 32, r);
                 tmem_ld_wait();
-                if (ch == BN / 32 - 1) {
+                if (c == kMyChunks - 1) {
                     // all of this thread's TMEM reads for the tile are done: release the accumulator buffer
                     tcgen05_fence_before();
                     mbar_arrive(&tmem_empty[buf]);
                 }
-                float v[32];
-#pragma unroll
-                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) + (p.bias ? __ldg(&p.bias[nt * BN + ch * 32 + j]) : 0.f);
+                // column block -> (tap, channel) : transposed conv scatters tap (dy, dx) to pixel (y*my + dy, x*mx + dx)
+                const int gcol = nt * BN + chunk * 32;
+                const int tap = gcol / p.tap_cout, c0 = gcol - tap * p.tap_cout;
+                const int dy = tap / p.mx, dx = tap - dy * p.mx;
+                DT *dst = opix + ((long long)dy * p.Wfull + dx) * p.out_ps + c0;
                 uint32_t pk[16];
 #pragma unroll
-                for (int j = 0; j < 16; ++j) pk[j] = pack2<DT>(v[2 * j], v[2 * j + 1]);
+                for (int k = 0; k < 8; ++k) {
+                    float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (p.bias) b = __ldg(reinterpret_cast<const float4 *>(p.bias + c0) + k);      // warp-uniform address
+                    pk[2 * k] = pack2<DT>(__uint_as_float(r[4 * k]) + b.x, __uint_as_float(r[4 * k + 1]) + b.y);
+                    pk[2 * k + 1] = pack2<DT>(__uint_as_float(r[4 * k + 2]) + b.z, __uint_as_float(r[4 * k + 3]) + b.w);
+                }
                 if (valid) {
-                    uint4 *dst = reinterpret_cast<uint4 *>(orow + ch * 32);
+                    // 2 x 32-byte stores (STG.256): every sector is written whole by one instruction
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) dst[j] = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+                    for (int k = 0; k < 2; ++k)
+                        asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst + 16 * k), "r"(pk[8 * k]), "r"(pk[8 * k + 1]),
+                                     "r"(pk[8 * k + 2]), "r"(pk[8 * k + 3]), "r"(pk[8 * k + 4]), "r"(pk[8 * k + 5]), "r"(pk[8 * k + 6]), "r"(pk[8 * k + 7]) : "memory");
                 }
                 if (do_stats) {
-                    float a[32], b[32];
+                    // statistics of the ROUNDED values (what the consumer normalises)
+                    if (kThreadAcc && fast_stats) {
+                        if (valid) {
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        const float2 f = unpack2<DT>(pk[j]);
-                        a[2 * j] = valid ? f.x : 0.f;
-                        a[2 * j + 1] = valid ? f.y : 0.f;
-                    }
-                    if (fast_stats) {
+                            for (int k = 0; k < 16; ++k) {
+                                const float2 f = unpack2<DT>(pk[k]);
+                                tacc1[2 * k] += f.x;
+                                tacc1[2 * k + 1] += f.y;
+                                tacc2[2 * k] = fmaf(f.x, f.x, tacc2[2 * k]);
+                                tacc2[2 * k + 1] = fmaf(f.y, f.y, tacc2[2 * k + 1]);
+                            }
+                        }
+                    } else {
+                        float a[32], b[32];
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) b[j] = a[j] * a[j];
-                        racc1[ch] += warp_transpose_sum32(a, lane);
-                        racc2[ch] += warp_transpose_sum32(b, lane);
-                    } else if (valid) {
-                        double *s = p.stats + ((long long)n * p.Cout + nt * BN + ch * 32) * 2;
+                        for (int k = 0; k < 16; ++k) {
+                            const float2 f = unpack2<DT>(pk[k]);
+                            a[2 * k] = valid ? f.x : 0.f;
+                            a[2 * k + 1] = valid ? f.y : 0.f;
+                        }
+                        if (fast_stats) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            atomicAdd(s + 2 * j, (double)a[j]);
-                            atomicAdd(s + 2 * j + 1, (double)a[j] * (double)a[j]);
+                            for (int k = 0; k < 32; ++k) b[k] = a[k] * a[k];
+                            racc1[c] += warp_transpose_sum32(a, lane);
+                            racc2[c] += warp_transpose_sum32(b, lane);
+                        } else if (valid) {
+                            // several images per tile (tiny levels): one atomic pair per value
+                            double *s = p.stats + ((long long)n * p.Cout + gcol) * 2;
+#pragma unroll
+                            for (int k = 0; k < 32; ++k) {
+                                atomicAdd(s + 2 * k, (double)a[k]);
+                                atomicAdd(s + 2 * k + 1, (double)a[k] * (double)a[k]);
+                            }
                         }
                     }
                 }
             }
-        }
-        if (fast_stats && cur_n >= 0) {
-#pragma unroll
-            for (int i = 0; i < BN / 32; ++i) {
-                double *s = p.stats + ((long long)cur_n * p.Cout + cur_nt * BN + i * 32 + lane) * 2;
-                atomicAdd(s, (double)racc1[i]);
-                atomicAdd(s + 1, (double)racc2[i]);
+            xt += estep;
+            while (xt >= p.tiles_w) {
+                xt -= p.tiles_w;
+                if (++yt == p.tiles_h) { yt = 0; if (++nn == p.tiles_n) { nn = 0; ++nt; } }
             }
         }
+        if (fast_stats && cur_n >= 0) flush_stats(cur_n, cur_nt);
     }
     tcgen05_fence_before();
     __syncthreads();

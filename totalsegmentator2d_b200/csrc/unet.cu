@@ -134,15 +134,19 @@ static void choose_tile(int Hout, int Wout, int N, int &tw, int &th, int &tn) {
     }
 }
 
-static int choose_bn(int cout, long long m_tiles) {
+// output-channel block of conv_tc_kernel from a cycle model of one CTA (measured on B200, tools/probe/mma_rate.cu:
+// an M=128, K=16 tcgen05.mma costs ~45 / 51 / 67 / 131 cycles at N = 32 / 64 / 128 / 256; an epilogue warp needs
+// ~400 cycles per 32-column chunk): time = waves x max(MMA time, epilogue time) per tile.
+static int choose_bn(int n_total, long long m_tiles, int k_steps) {
     int best_bn = 32;
-    double best_eff = -1;
+    double best = 1e30;
     for (int bn : {256, 128, 64, 32}) {
-        if (cout % bn) continue;
-        const long long tiles = m_tiles * (cout / bn);
-        const double eff = (double)tiles / ((double)ceil_div(tiles, kNumSMs) * kNumSMs);
-        // larger BN halves the A re-reads; require a clear occupancy win to go smaller
-        if (eff > best_eff * 1.15) { best_eff = eff; best_bn = bn; }
+        if (n_total % bn) continue;
+        const double mma = bn == 256 ? 131 : bn == 128 ? 67 : bn == 64 ? 51 : 45;
+        const double epi = bn == 32 ? 200 : 400.0 * (bn / 64);
+        const long long tiles = m_tiles * (n_total / bn);
+        const double t = (double)ceil_div(tiles, kNumSMs) * std::max(k_steps * mma, epi) + 0.02 * k_steps * mma * (n_total / bn);   // tie-break: fewer A re-reads
+        if (t < best) { best = t; best_bn = bn; }
     }
     return best_bn;
 }
@@ -184,7 +188,7 @@ static int encode_w_map(CUtensorMap *tm, const void *base, int Cin, int Cout, in
 }
 
 template <int BN, int KC, typename DT>
-static int launch_tc_inst(const CUtensorMap &tmA, const CUtensorMap &tmB, const ConvTcParams &p, int grid_y, cudaStream_t st) {
+static int launch_tc_inst(const CUtensorMap &tmA, const CUtensorMap &tmB, const ConvTcParams &p, cudaStream_t st) {
     static bool attr_set = false;
     constexpr int smem = tc_smem_bytes<BN, KC>();
     if (!attr_set) {
@@ -193,14 +197,14 @@ static int launch_tc_inst(const CUtensorMap &tmA, const CUtensorMap &tmB, const 
     }
     const int m_tiles = p.tiles_n * p.tiles_h * p.tiles_w;
     const int total = m_tiles * p.n_tiles_n;
-    const int gx = std::max(1, std::min(total, kNumSMs / grid_y));
-    conv_tc_kernel<BN, KC, DT><<<dim3(gx, grid_y), 192, smem, st>>>(tmA, tmB, p);
+    const int gx = std::max(1, std::min(total, kNumSMs));
+    conv_tc_kernel<BN, KC, DT><<<gx, kTcThreads, smem, st>>>(tmA, tmB, p);
     TS2D_LAUNCH_CHECK();
     return TS2D_OK;
 }
 template <typename DT>
-static int launch_tc(int bn, int kc, const CUtensorMap &tmA, const CUtensorMap &tmB, const ConvTcParams &p, int grid_y, cudaStream_t st) {
-#define TS2D_TC_CASE(B, K) if (bn == B && kc == K) return launch_tc_inst<B, K, DT>(tmA, tmB, p, grid_y, st);
+static int launch_tc(int bn, int kc, const CUtensorMap &tmA, const CUtensorMap &tmB, const ConvTcParams &p, cudaStream_t st) {
+#define TS2D_TC_CASE(B, K) if (bn == B && kc == K) return launch_tc_inst<B, K, DT>(tmA, tmB, p, st);
     TS2D_TC_CASE(32, 32) TS2D_TC_CASE(64, 32) TS2D_TC_CASE(128, 32) TS2D_TC_CASE(256, 32)
     TS2D_TC_CASE(32, 64) TS2D_TC_CASE(64, 64) TS2D_TC_CASE(128, 64) TS2D_TC_CASE(256, 64)
 #undef TS2D_TC_CASE
@@ -367,6 +371,7 @@ static void fill_tc_params(ConvTcParams &p, int N, int Hout, int Wout, int cout,
     p.stride2 = stride2 ? 1 : 0;
     p.in_ps = (int)in_ps;
     p.n_tiles_n = cout / bn;
+    p.tap_cout = cout;
     p.my = 1; p.mx = 1; p.Hfull = Hout; p.Wfull = Wout;
 }
 
@@ -686,7 +691,7 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
         int tw, th, tn;
         choose_tile(c.Hout, c.Wout, N, tw, th, tn);
         const long long m_tiles = (long long)ceil_div(c.Wout, tw) * ceil_div(c.Hout, th) * ceil_div(N, tn);
-        const int bn = choose_bn(c.cout, m_tiles);
+        const int bn = choose_bn(c.cout, m_tiles, c.kh * c.kw * c.cin / 16);
         fill_tc_params(p, N, c.Hout, c.Wout, c.cout, c.cin, c.kc, bn, c.kh * c.kw, c.kw, (c.kh - 1) / 2, (c.kw - 1) / 2, s2, c.in_ps);
         p.tw = tw; p.th = th; p.tn = tn;
         p.tiles_w = ceil_div(c.Wout, tw); p.tiles_h = ceil_div(c.Hout, th); p.tiles_n = ceil_div(N, tn);
@@ -698,7 +703,7 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
             c.bn = bn;
             c.enc_n = N;
         }
-        rc = is_bf16 ? launch_tc<__nv_bfloat16>(bn, c.kc, c.tmA, c.tmB, p, 1, st) : launch_tc<__half>(bn, c.kc, c.tmA, c.tmB, p, 1, st);
+        rc = is_bf16 ? launch_tc<__nv_bfloat16>(bn, c.kc, c.tmA, c.tmB, p, st) : launch_tc<__half>(bn, c.kc, c.tmA, c.tmB, p, st);
         if (rc) return rc;
     } else if (c.first_fast) {
         FirstConvParams p;
@@ -755,20 +760,22 @@ static int run_up(ts2d_unet *u, UpLayer &up, int N, cudaStream_t st) {
         choose_tile(up.Hin, up.Win, N, tw, th, tn);
         const long long m_tiles = (long long)ceil_div(up.Win, tw) * ceil_div(up.Hin, th) * ceil_div(N, tn);
         const int taps = up.sh * up.sw;
-        const int bn = choose_bn(up.cout, m_tiles * taps);
-        fill_tc_params(p, N, up.Hin, up.Win, up.cout, up.cin, up.kc, bn, 1, 1, 0, 0, false, up.cin);
+        // GEMM N axis = (tap, Cout): all taps of a pixel in one pass over A; the epilogue scatters column block (tap, c0)
+        const int n_total = taps * up.cout;
+        const int bn = choose_bn(n_total, m_tiles, up.cin / 16);
+        fill_tc_params(p, N, up.Hin, up.Win, n_total, up.cin, up.kc, bn, 1, 1, 0, 0, false, up.cin);
+        p.tap_cout = up.cout;
         p.tw = tw; p.th = th; p.tn = tn;
         p.tiles_w = ceil_div(up.Win, tw); p.tiles_h = ceil_div(up.Hin, th); p.tiles_n = ceil_div(N, tn);
         p.my = up.sh; p.mx = up.sw; p.Hfull = up.Hin * up.sh; p.Wfull = up.Win * up.sw;
         p.out_ps = up.out_ps; p.out = up.out; p.bias = up.b.dev; p.stats = nullptr;
-        p.tap_base_from_grid_y = 1;
         if (up.bn != bn || up.enc_n != N) {
             if ((rc = encode_act_map(&up.tmA, up.in, up.cin, up.cin, up.Hin, up.Win, pl.max_batch, false, up.kc, tw, th, tn, es, is_bf16))) return rc;
-            if ((rc = encode_w_map(&up.tmB, up.w_tc, up.cin, up.cout, taps, up.kc, bn, es, is_bf16))) return rc;
+            if ((rc = encode_w_map(&up.tmB, up.w_tc, up.cin, n_total, 1, up.kc, bn, es, is_bf16))) return rc;      // [tap][Cout][Cin] viewed as [taps*Cout][Cin]
             up.bn = bn;
             up.enc_n = N;
         }
-        rc = is_bf16 ? launch_tc<__nv_bfloat16>(bn, up.kc, up.tmA, up.tmB, p, taps, st) : launch_tc<__half>(bn, up.kc, up.tmA, up.tmB, p, taps, st);
+        rc = is_bf16 ? launch_tc<__nv_bfloat16>(bn, up.kc, up.tmA, up.tmB, p, st) : launch_tc<__half>(bn, up.kc, up.tmA, up.tmB, p, st);
         if (rc) return rc;
         u->launches++;
     } else {
@@ -871,7 +878,7 @@ template <typename T, int CAP>
 static int launch_blend(const BlendParams &p, const int *tile_yx_host, int F, cudaStream_t st) {
     const long long npix = (long long)p.h * p.w;
     const int grid = ceil_div(npix, 128);
-    const size_t smem = (size_t)(p.heads * F + p.heads) * sizeof(float);
+    const size_t smem = (size_t)(p.heads * F + p.heads) * sizeof(float) + (size_t)128 * p.heads;
     TileListT<CAP> tl;
     fill_tile_list(tl, tile_yx_host, p.T);
     switch (F) {

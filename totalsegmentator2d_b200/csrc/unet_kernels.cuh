@@ -285,13 +285,16 @@ struct BlendParams {
 
 template <typename T, int F, int CAP>
 __global__ void __launch_bounds__(128) blend_head_kernel(const BlendParams p, const __grid_constant__ TileListT<CAP> tl) {
-    extern __shared__ float s_head[];            // head_w [heads][F] then head_b[heads]
+    extern __shared__ float s_head[];            // head_w [heads][F], head_b [heads], then the block's mask bytes [128][heads]
+    uint8_t *s_mask = reinterpret_cast<uint8_t *>(s_head + p.heads * F + p.heads);
     for (int i = threadIdx.x; i < p.heads * F; i += blockDim.x) s_head[i] = p.head_w[i];
     for (int i = threadIdx.x; i < p.heads; i += blockDim.x) s_head[p.heads * F + i] = p.head_b ? p.head_b[i] : 0.f;
     __syncthreads();
-    const long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (pix >= (long long)p.h * p.w) return;
-    const int y = (int)(pix / p.w), x = (int)(pix % p.w);
+    const long long npix = (long long)p.h * p.w;
+    const long long pix0 = (long long)blockIdx.x * blockDim.x;
+    const long long pix = pix0 + threadIdx.x;
+    const bool active = pix < npix;
+    const int y = active ? (int)(pix / p.w) : 0, x = active ? (int)(pix % p.w) : 0;
     const int yp = y + p.pad_top, xp = x + p.pad_left;
     float acc[F];
 #pragma unroll
@@ -299,7 +302,7 @@ __global__ void __launch_bounds__(128) blend_head_kernel(const BlendParams p, co
     float wsum = 0.f;
     const T *feat = reinterpret_cast<const T *>(p.feat);
     const float inv_m = 1.0f / (float)p.M;
-    for (int t = 0; t < p.T; ++t) {
+    for (int t = 0; t < p.T && active; ++t) {
         const int ly = yp - tl.yx[t][0], lx = xp - tl.yx[t][1];
         if (ly < 0 || ly >= p.Ph || lx < 0 || lx >= p.Pw) continue;
         const float g = p.gauss[ly * p.Pw + lx];
@@ -312,39 +315,70 @@ __global__ void __launch_bounds__(128) blend_head_kernel(const BlendParams p, co
             else if (p.mirror_mask == 2) fw = (m == 1);
             const int sy = fh ? p.Ph - 1 - ly : ly, sx = fw ? p.Pw - 1 - lx : lx;
             const T *f = feat + (((long long)(t * p.M + m) * p.Ph + sy) * p.Pw + sx) * F;
-            if (p.feat_ss) {
-                const float2 *ss = reinterpret_cast<const float2 *>(p.feat_ss) + (long long)(t * p.M + m) * F;     // warp-uniform: broadcast loads
-#pragma unroll
-                for (int k = 0; k < F; ++k) {
-                    const float2 c = __ldg(ss + k);
-                    float y = fmaf(to_f32<T>(f[k]), c.x, c.y);
-                    y = y > 0.f ? y : y * p.slope;
-                    acc[k] = fmaf(gm, to_f32<T>(from_f32<T>(y)), acc[k]);
-                }
-            } else if constexpr (sizeof(T) == 2 && (F % 8) == 0) {
+            if constexpr (sizeof(T) == 2 && (F % 8) == 0) {
+                const float4 *ss = reinterpret_cast<const float4 *>(p.feat_ss) + (long long)(t * p.M + m) * (F / 2);    // {sc, sh, sc, sh}: warp-uniform broadcast loads
 #pragma unroll
                 for (int k = 0; k < F; k += 8) {
                     uint4 v = *reinterpret_cast<const uint4 *>(f + k);
                     const T *e = reinterpret_cast<const T *>(&v);
+                    if (p.feat_ss) {
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) acc[k + j] = fmaf(gm, to_f32<T>(e[j]), acc[k + j]);
+                        for (int j = 0; j < 8; j += 2) {
+                            const float4 c = __ldg(ss + (k + j) / 2);
+                            float y0 = fmaf(to_f32<T>(e[j]), c.x, c.y), y1 = fmaf(to_f32<T>(e[j + 1]), c.z, c.w);
+                            y0 = y0 > 0.f ? y0 : y0 * p.slope;
+                            y1 = y1 > 0.f ? y1 : y1 * p.slope;
+                            acc[k + j] = fmaf(gm, to_f32<T>(from_f32<T>(y0)), acc[k + j]);          // rounded to T like norm_act_kernel's output
+                            acc[k + j + 1] = fmaf(gm, to_f32<T>(from_f32<T>(y1)), acc[k + j + 1]);
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) acc[k + j] = fmaf(gm, to_f32<T>(e[j]), acc[k + j]);
+                    }
                 }
             } else {
+                const float2 *ss = reinterpret_cast<const float2 *>(p.feat_ss) + (long long)(t * p.M + m) * F;
 #pragma unroll
-                for (int k = 0; k < F; ++k) acc[k] = fmaf(gm, to_f32<T>(f[k]), acc[k]);
+                for (int k = 0; k < F; ++k) {
+                    float v = to_f32<T>(f[k]);
+                    if (p.feat_ss) {
+                        const float2 c = __ldg(ss + k);
+                        v = fmaf(v, c.x, c.y);
+                        v = v > 0.f ? v : v * p.slope;
+                        v = to_f32<T>(from_f32<T>(v));
+                    }
+                    acc[k] = fmaf(gm, v, acc[k]);
+                }
             }
         }
     }
     const float inv = 1.0f / wsum;
 #pragma unroll
     for (int k = 0; k < F; ++k) acc[k] *= inv;
+    const int lane = threadIdx.x & 31;
     for (int c = 0; c < p.heads; ++c) {
         float v = s_head[p.heads * F + c];
 #pragma unroll
         for (int k = 0; k < F; ++k) v = fmaf(s_head[c * F + k], acc[k], v);
-        if (p.logits) p.logits[((long long)c * p.h + y) * p.w + x] = v;
-        if (p.mask) p.mask[((long long)(p.h0 + y) * p.W0 + (p.w0 + x)) * p.ch_total + p.ch_off + c] = v > 0.f ? 1 : 0;
-        if (p.present && v > 0.f) p.present[p.ch_off + c] = 1;
+        const bool on = active && v > 0.f;
+        if (p.logits && active) p.logits[((long long)c * p.h + y) * p.w + x] = v;
+        if (p.mask) s_mask[threadIdx.x * p.heads + c] = on ? 1 : 0;
+        if (p.present) {
+            const unsigned any = __ballot_sync(0xffffffffu, on);
+            if (any && lane == 0) p.present[p.ch_off + c] = 1;
+        }
+    }
+    if (p.mask) {
+        // the block's 128 pixels x heads bytes leave through shared memory so that consecutive threads write consecutive bytes
+        // of a pixel's channel window (runs of `heads` bytes at a pitch of ch_total) instead of 32 scattered bytes per store
+        __syncthreads();
+        const int n_here = (int)min((long long)blockDim.x, npix - pix0);
+        for (int i = threadIdx.x; i < n_here * p.heads; i += blockDim.x) {
+            const int pp = i / p.heads, c = i - pp * p.heads;
+            const long long gp = pix0 + pp;
+            const int yy = (int)(gp / p.w), xx = (int)(gp % p.w);
+            p.mask[((long long)(p.h0 + yy) * p.W0 + (p.w0 + xx)) * p.ch_total + p.ch_off + c] = s_mask[i];
+        }
     }
 }
 
