@@ -161,6 +161,11 @@ int ts2d_threshold_logits(const float *logits_dev, int heads, int h, int w, int 
  * perm_host: int[C]. */
 int ts2d_permute_channels(const uint8_t *src_dev, uint8_t *dst_dev, int64_t n_pix, int C, const int *perm_host,
                           ts2d_stream stream);
+/* the same with the reference's merged order computed on the device (no host round trip between the models and the merge):
+ * per model window offsets_host[m]..offsets_host[m+1], labels with present_dev[c] != 0 first (ascending), then the absent ones.
+ * perm_dev: int32[C], receives the permutation (the host reads it to name the channels). */
+int ts2d_merge_present_order(const uint8_t *src_dev, uint8_t *dst_dev, int64_t n_pix, int C, const uint8_t *present_dev,
+                             const int *offsets_host, int n_models, int *perm_dev, ts2d_stream stream);
 /* re-allocates the workspace for a larger/smaller max_batch (weights are kept) */
 int ts2d_unet_resize(ts2d_unet *u, int max_batch);
 /* number of kernel launches this engine issued since creation (bench.py's gpu_launches) */

@@ -94,3 +94,45 @@ def test_save_writes_reference_file_names(zoo, tmp_path):
         assert os.path.exists(os.path.join(str(tmp_path), fn)), fn
     seg = nrrd.read_nrrd(os.path.join(str(tmp_path), f"{s}.seg.nrrd"))
     assert seg.GetSize() == (53, 1, 133) and seg.HasMetaDataKey("Segment0_Name") and seg.GetMetaData("Segment0_LabelValue") == "1"
+
+
+def test_predict_batch_pipeline_equals_predict(zoo):
+    """the 3-stream pipelined batch API returns, in input order, exactly what predict() returns study by study"""
+    from totalsegmentator2d_b200.image import Image
+    from totalsegmentator2d_b200.tool import TS2D
+    root, groups = zoo
+    imgs = []
+    for i, shape in enumerate([(90, 20, 70), (130, 24, 64), (70, 16, 100), (90, 20, 70)]):
+        vol = torch.from_numpy(synthetic_ct(shape, seed=50 + i)).pin_memory()
+        imgs.append(Image(vol.numpy(), (1.5, 1.5, 1.5), (0.0, 0.0, 0.0), np.eye(3).reshape(-1)))
+    with TS2D(key="ts2d", models_root=root, param={"b200.precision": "bf16"}) as ts:
+        single = [ts.predict(im) for im in imgs]
+        batched = list(ts.predict_batch(imgs, depth=3))
+        assert len(batched) == len(imgs)
+        for a, b in zip(single, batched):
+            sa, sb = a.get_segmentation(), b.get_segmentation()
+            assert np.array_equal(np.asarray(sa.array), np.asarray(sb.array))
+            assert sa.GetMetaDataKeys() == sb.GetMetaDataKeys() and all(sa.GetMetaData(k) == sb.GetMetaData(k) for k in sa.GetMetaDataKeys())
+            for m in a.models:
+                assert np.array_equal(np.asarray(a.get_segmentation(m).array), np.asarray(b.get_segmentation(m).array))
+            for k in a.get_projection():
+                assert np.array_equal(np.asarray(a.get_projection(k).array), np.asarray(b.get_projection(k).array))
+
+
+def test_merge_present_order_on_device():
+    """ts2d_merge_present_order == host permutation with labels present first per model (reference meta.py:280-286)"""
+    from totalsegmentator2d_b200 import ops
+    g = torch.Generator().manual_seed(3)
+    for n_pix, offs in [(1000, [0, 5, 12, 30]), (128 * 7, [0, 18, 41, 65, 91, 117]), (77, [0, 3])]:
+        C = offs[-1]
+        src = (torch.rand(n_pix, C, generator=g) > 0.5).to(torch.uint8).cuda()
+        present = (torch.rand(C, generator=g) > 0.4).to(torch.uint8).cuda()
+        out, perm = ops.merge_present_order(src, present, offs)
+        p = present.cpu().numpy().astype(bool)
+        want = []
+        for m in range(len(offs) - 1):
+            cs = list(range(offs[m], offs[m + 1]))
+            want += [c for c in cs if p[c]] + [c for c in cs if not p[c]]
+        assert perm.cpu().tolist() == want
+        assert torch.equal(out.cpu(), src.cpu()[:, want])
+        assert torch.equal(ops.permute_channels(src, want).cpu(), src.cpu()[:, want])

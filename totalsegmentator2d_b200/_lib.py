@@ -51,6 +51,7 @@ class TS2DError(RuntimeError):
 
 
 _lib: Optional[C.CDLL] = None
+_checked_devices = set()
 
 _vp, _i, _i64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_float
 _ip = C.POINTER(C.c_int)
@@ -76,6 +77,7 @@ _PROTOS = {
     "ts2d_unet_blend_head": (_i, [_vp, _ip, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp]),
     "ts2d_threshold_logits": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "ts2d_permute_channels": (_i, [_vp, _vp, _i64, _i, _ip, _vp]),
+    "ts2d_merge_present_order": (_i, [_vp, _vp, _i64, _i, _vp, _ip, _i, _vp, _vp]),
     "ts2d_unet_launch_count": (_i64, [_vp]),
     "ts2d_unet_flops": (C.c_double, [_vp, _i]),
     "ts2d_unet_set_profiling": (_i, [_vp, _i]),
@@ -105,7 +107,10 @@ def load(check_device: bool = False) -> C.CDLL:
         import torch
         if not torch.cuda.is_available():
             raise TS2DError("no CUDA device: the TS2D hot path runs on an sm_100 (B200) GPU only")
-        check(_lib.ts2d_device_check(torch.cuda.current_device()))
+        dev = torch.cuda.current_device()
+        if dev not in _checked_devices:
+            check(_lib.ts2d_device_check(dev))
+            _checked_devices.add(dev)
     return _lib
 
 

@@ -74,8 +74,8 @@ def _to_device(arr: np.ndarray) -> torch.Tensor:
         return arr.cuda(non_blocking=True).contiguous()
     a = np.ascontiguousarray(arr)
     if a.dtype == np.uint16:
-        return torch.from_numpy(a.view(np.int16)).cuda().view(torch.uint16)
-    return torch.from_numpy(a).cuda()
+        return torch.from_numpy(a.view(np.int16)).cuda(non_blocking=True).view(torch.uint16)
+    return torch.from_numpy(a).cuda(non_blocking=True)      # asynchronous when the array lives in pinned memory
 
 
 def reorient_image(img: Image, orient: str = "RAI") -> Image:

@@ -934,6 +934,14 @@ extern "C" int ts2d_unet_blend_head(ts2d_unet *u, const int *tile_yx_host, int T
     return TS2D_OK;
 }
 
+static int launch_permute(const uint8_t *src, uint8_t *dst, int64_t n_pix, const PermList &pl, const int *perm_dev, cudaStream_t st) {
+    if (n_pix == 0) return TS2D_OK;
+    const int grid = (int)((n_pix + 127) / 128);
+    permute_channels_kernel<<<grid, 128, 128 * pl.C + pl.C + 16, st>>>(src, dst, n_pix, pl, perm_dev);
+    TS2D_LAUNCH_CHECK();
+    return TS2D_OK;
+}
+
 extern "C" int ts2d_permute_channels(const uint8_t *src_dev, uint8_t *dst_dev, int64_t n_pix, int C, const int *perm_host, ts2d_stream stream) {
     TS2D_REQUIRE(src_dev && dst_dev && perm_host && src_dev != dst_dev, "ts2d_permute_channels: bad pointers");
     TS2D_REQUIRE(C >= 1 && C <= 256 && n_pix >= 0, "ts2d_permute_channels: C must be 1..256");
@@ -943,11 +951,26 @@ extern "C" int ts2d_permute_channels(const uint8_t *src_dev, uint8_t *dst_dev, i
         TS2D_REQUIRE(perm_host[j] >= 0 && perm_host[j] < C, "ts2d_permute_channels: perm[%d] out of range", j);
         pl.perm[j] = perm_host[j];
     }
-    if (n_pix == 0) return TS2D_OK;
-    const int grid = (int)std::min<long long>(((long long)n_pix * C + 255) / 256, (long long)kNumSMs * 16);
-    permute_channels_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src_dev, dst_dev, n_pix, pl);
+    return launch_permute(src_dev, dst_dev, n_pix, pl, nullptr, (cudaStream_t)stream);
+}
+
+extern "C" int ts2d_merge_present_order(const uint8_t *src_dev, uint8_t *dst_dev, int64_t n_pix, int C, const uint8_t *present_dev,
+                                        const int *offsets_host, int n_models, int *perm_dev, ts2d_stream stream) {
+    TS2D_REQUIRE(src_dev && dst_dev && present_dev && offsets_host && perm_dev && src_dev != dst_dev, "ts2d_merge_present_order: bad pointers");
+    TS2D_REQUIRE(C >= 1 && C <= 256 && n_pix >= 0 && n_models >= 1 && n_models <= 32, "ts2d_merge_present_order: C must be 1..256, models 1..32");
+    TS2D_REQUIRE(offsets_host[0] == 0 && offsets_host[n_models] == C, "ts2d_merge_present_order: offsets must cover [0, C)");
+    ModelOffsets mo;
+    mo.n_models = n_models;
+    for (int m = 0; m <= n_models; ++m) {
+        TS2D_REQUIRE(m == 0 || offsets_host[m] >= offsets_host[m - 1], "ts2d_merge_present_order: offsets must be ascending");
+        mo.off[m] = offsets_host[m];
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    present_order_kernel<<<1, 32, 0, st>>>(present_dev, mo, perm_dev);
     TS2D_LAUNCH_CHECK();
-    return TS2D_OK;
+    PermList pl;
+    pl.C = C;
+    return launch_permute(src_dev, dst_dev, n_pix, pl, perm_dev, st);
 }
 
 extern "C" int ts2d_unet_resize(ts2d_unet *u, int max_batch) {

@@ -396,14 +396,51 @@ __global__ void __launch_bounds__(128) tile_logits_kernel(const T *feat, int F, 
     }
 }
 
-// dst[pix][j] = src[pix][perm[j]]
+// dst[pix][j] = src[pix][perm[j]]  (channel order of combine_segmentations, reference ts2d/core/util/image.py:490-510)
+// A block moves 128 pixels: 128*C contiguous bytes in (16-byte loads), permuted inside shared memory, 128*C contiguous
+// bytes out (4-byte stores).  perm comes from kernel-parameter space (host order) or from device memory (present order).
 struct PermList { int C; int perm[256]; };
-__global__ void __launch_bounds__(256) permute_channels_kernel(const uint8_t *src, uint8_t *dst, long long n, PermList pl) {
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n * pl.C; i += (long long)gridDim.x * blockDim.x) {
-        const long long pix = i / pl.C;
-        const int j = (int)(i % pl.C);
-        dst[i] = src[pix * pl.C + pl.perm[j]];
+__global__ void __launch_bounds__(128) permute_channels_kernel(const uint8_t *src, uint8_t *dst, long long n, const __grid_constant__ PermList pl,
+                                                               const int *perm_dev) {
+    extern __shared__ __align__(16) uint8_t s_px[];      // [128][C] then perm as bytes [C]
+    const int C = pl.C;
+    uint8_t *s_perm = s_px + 128 * C;
+    for (int j = threadIdx.x; j < C; j += blockDim.x) s_perm[j] = (uint8_t)(perm_dev ? perm_dev[j] : pl.perm[j]);
+    const long long p0 = (long long)blockIdx.x * 128;
+    const int np = (int)min(128LL, n - p0);
+    const long long bytes = (long long)np * C;
+    const uint8_t *g = src + p0 * C;
+    if (np == 128) {     // 128*C is a multiple of 16 and the block base a multiple of 128 bytes
+        for (int i = threadIdx.x; i < 8 * C; i += blockDim.x) reinterpret_cast<uint4 *>(s_px)[i] = __ldg(reinterpret_cast<const uint4 *>(g) + i);
+    } else {
+        for (int i = threadIdx.x; i < bytes; i += blockDim.x) s_px[i] = g[i];
     }
+    __syncthreads();
+    uint8_t *o = dst + p0 * C;
+    if (np == 128) {
+        for (int w = threadIdx.x; w < 32 * C; w += blockDim.x) {
+            uint32_t v = 0;
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                const int i = 4 * w + b, px = i / C, j = i - px * C;
+                v |= (uint32_t)s_px[px * C + s_perm[j]] << (8 * b);
+            }
+            reinterpret_cast<uint32_t *>(o)[w] = v;
+        }
+    } else {
+        for (int i = threadIdx.x; i < bytes; i += blockDim.x) { const int px = i / C, j = i - px * C; o[i] = s_px[px * C + s_perm[j]]; }
+    }
+}
+
+// perm for the reference's merged channel order: per model, labels present in the image first (ascending), then the absent
+// ones (reference ts2d/core/util/meta.py:280-286).  One thread per model; offsets[m]..offsets[m+1] is model m's channel window.
+struct ModelOffsets { int n_models; int off[33]; };
+__global__ void present_order_kernel(const uint8_t *present, const __grid_constant__ ModelOffsets mo, int *perm) {
+    const int m = threadIdx.x;
+    if (m >= mo.n_models) return;
+    int k = mo.off[m];
+    for (int c = mo.off[m]; c < mo.off[m + 1]; ++c) if (present[c]) perm[k++] = c;
+    for (int c = mo.off[m]; c < mo.off[m + 1]; ++c) if (!present[c]) perm[k++] = c;
 }
 
 // NHWC (pixel stride ps) -> float32 NCHW (layer-wise parity tests)

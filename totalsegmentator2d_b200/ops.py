@@ -133,5 +133,18 @@ def permute_channels(src: torch.Tensor, perm: Sequence[int], out: Optional[torch
     return out
 
 
+def merge_present_order(src: torch.Tensor, present: torch.Tensor, offsets: Sequence[int], out: Optional[torch.Tensor] = None):
+    """combine_segmentations channel order (labels present in the image first, per model) computed and applied on the device.
+    Returns (merged mask, perm int32[C] on the device)."""
+    lib = L.load()
+    Cc = src.shape[-1]
+    if out is None:
+        out = torch.empty_like(src)
+    perm = torch.empty(Cc, dtype=torch.int32, device=src.device)
+    L.check(lib.ts2d_merge_present_order(_dev(src, "src"), _dev(out, "out"), src.numel() // Cc, Cc, _dev(present, "present"),
+                                         L.int_array(list(offsets)), len(offsets) - 1, perm.data_ptr(), L.stream_ptr()), "ts2d_merge_present_order")
+    return out, perm
+
+
 def torch_dtype_of(precision: int):
     return _PREC_TO_TORCH[precision]

@@ -180,51 +180,132 @@ class TS2D:
         :param collapse: collapse the output image and segmentation to 2D (discards the 3D orientation)
         :param merge: merge the individual model segmentations into a single segmentation image
         """
+        return self._finish(self._submit(input, collapse, merge))
+
+    def predict_batch(self, inputs, collapse: bool = False, merge: bool = True, depth: int = 2):
+        """Generator over ``predict`` results for a sequence of inputs (the reference CLI loops over its inputs one by one,
+        ts2d/main.py:80-83).  Software pipeline over three CUDA streams: while study i computes, study i+1 is uploaded and
+        the mask of study i-1 is downloaded and wrapped on the host.  Results come out in input order."""
+        pending = []
+        for inp in inputs:
+            pending.append(self._submit(inp, collapse, merge))
+            if len(pending) >= max(1, depth):
+                yield self._finish(pending.pop(0))
+        while pending:
+            yield self._finish(pending.pop(0))
+
+    def _streams(self):
+        if getattr(self, "_h2d_stream", None) is None:
+            self._h2d_stream = torch.cuda.Stream()
+            self._d2h_stream = torch.cuda.Stream()
+        return self._h2d_stream, self._d2h_stream
+
+    @staticmethod
+    def _pinned_like(t: torch.Tensor) -> torch.Tensor:
+        return torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+
+    def _submit(self, input, collapse: bool, merge: bool) -> dict:
+        """enqueues upload, device pipeline and download of one input; nothing here waits for the GPU"""
         if isinstance(input, str):
             input = read_image(input)
         try:
             input = from_sitk(input)
         except RuntimeError:
             raise RuntimeError(f"input must be a string path or a SimpleITK image, found: {type(input).__name__}")
-
         ids = list(self.models.keys())
         is3d = get_actual_dimension(input) > 2
         chan_defs = self._channel_defs()
-
-        result = dict()
-        projections: Dict[str, Image] = dict()
+        h2d, d2h = self._streams()
+        cur = torch.cuda.current_stream()
+        job = {"input": input, "collapse": collapse, "merge": merge, "is3d": is3d, "chan_defs": chan_defs, "keep": []}
         if is3d:
-            vol = _to_device(input.array)
-            perm, flip = orientation_remap(input.direction_matrix(), "RAI")
-            size, sp, org, nd = _reoriented_geometry(input, perm, flip)
-            ax = axis_name_to_index("coronal")
+            with torch.cuda.stream(h2d):
+                vol = _to_device(input.array)
+                ev = torch.cuda.Event()
+                ev.record(h2d)
+            cur.wait_event(ev)
+            vol.record_stream(cur)
             dev = self.predict_volume_device(vol, input.GetSpacing(), input.direction_matrix())
             del vol
-            host = dev["projections"].cpu().numpy()
-            for i, n in enumerate(dev["channel_names"]):
-                projections[n] = _projected_image(host[i], size, sp, org, nd, ax)
         else:
             base2d = input if input.GetDimension() < 3 else reduce_dimensions(input)
-            chs = split_channels(input)
-            projections.update((f"ch{i}", ch) for i, ch in enumerate(chs))
             input_nch = input.GetNumberOfComponentsPerPixel()
             for id in ids:
                 if len(chan_defs[id]) != input_nch:
                     raise RuntimeError(f"The number of channels in the input image does not match the models channel definition ({len(chan_defs[id])} vs {input_nch}).")
             arr = np.asarray(base2d.array, dtype=np.float32)
             chw = np.moveaxis(arr, -1, 0) if base2d.is_vector else arr[None]
-            img_dev_2d = torch.from_numpy(np.ascontiguousarray(chw)).cuda()
+            with torch.cuda.stream(h2d):
+                img_dev_2d = torch.from_numpy(np.ascontiguousarray(chw)).cuda(non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(h2d)
+            cur.wait_event(ev)
+            img_dev_2d.record_stream(cur)
             dev = self.predict_image_device({id: img_dev_2d for id in ids}, base2d.GetSpacing())
+            job["base2d"] = base2d
         mask, present, offs = dev["mask"], dev["present"], dev["offsets"]
+        job.update(mask=mask, offs=offs, channel_names=dev.get("channel_names"))
+        merged_dev = perm_dev = None
+        if merge and len(ids) > 1:
+            # channel order of combine_segmentations (present labels first) computed and applied on the device
+            merged_dev, perm_dev = ops.merge_present_order(mask, present, offs)
+        ev_c = torch.cuda.Event()
+        ev_c.record(cur)
+        with torch.cuda.stream(d2h):
+            d2h.wait_event(ev_c)
+            if is3d:
+                job["proj_host"] = self._pinned_like(dev["projections"])
+                job["proj_host"].copy_(dev["projections"], non_blocking=True)
+                dev["projections"].record_stream(d2h)
+            if merged_dev is not None:
+                job["merged_host"] = self._pinned_like(merged_dev)
+                job["merged_host"].copy_(merged_dev, non_blocking=True)
+                job["perm_host"] = self._pinned_like(perm_dev)
+                job["perm_host"].copy_(perm_dev, non_blocking=True)
+                merged_dev.record_stream(d2h)
+                perm_dev.record_stream(d2h)
+            elif merge:
+                lo, hi = int(offs[0]), int(offs[1])
+                single = mask[..., lo:hi].contiguous() if (hi - lo) != mask.shape[-1] else mask
+                job["merged_host"] = self._pinned_like(single)
+                job["merged_host"].copy_(single, non_blocking=True)
+                single.record_stream(d2h)
+            ev_d = torch.cuda.Event()
+            ev_d.record(d2h)
+        job["done"] = ev_d
+        return job
+
+    def _finish(self, job: dict):
+        """waits for the download of one submitted input and wraps it like reference tool.py:108-129"""
+        input, collapse, merge, is3d, chan_defs = job["input"], job["collapse"], job["merge"], job["is3d"], job["chan_defs"]
+        ids = list(self.models.keys())
+        mask, offs = job["mask"], job["offs"]
+        job["done"].synchronize()
+        result = dict()
+        projections: Dict[str, Image] = dict()
+        if is3d:
+            perm, flip = orientation_remap(input.direction_matrix(), "RAI")
+            size, sp, org, nd = _reoriented_geometry(input, perm, flip)
+            ax = axis_name_to_index("coronal")
+            host = job["proj_host"].numpy()
+            for i, n in enumerate(job["channel_names"]):
+                projections[n] = _projected_image(host[i], size, sp, org, nd, ax)
+        else:
+            chs = split_channels(input)
+            projections.update((f"ch{i}", ch) for i, ch in enumerate(chs))
 
         model_inputs = dict()
+        composed = dict()
         for k, id in enumerate(ids):
             model = self.models[id]
             res = {"id": id, "revision": model.revision}
             res["model"], res["group"] = decompose_model_key(id)
             if is3d:
-                ch_list = [projections[n] for _, n in chan_defs[id]]
-                minput = compose(ch_list) if len(ch_list) > 1 else ch_list[0]
+                names = tuple(n for _, n in chan_defs[id])
+                if names not in composed:      # models with the same channel definition share one composed input image
+                    ch_list = [projections[n] for n in names]
+                    composed[names] = compose(ch_list) if len(ch_list) > 1 else ch_list[0]
+                minput = composed[names]
             else:
                 minput = input
             native_2d = minput.GetDimension() < 3
@@ -247,25 +328,25 @@ class TS2D:
 
         if merge:
             if len(ids) == 1:
-                result["segmentation"] = result["models"][ids[0]]["segmentation"].materialize()
+                seg = result["models"][ids[0]]["segmentation"]
+                seg._img = seg.finish(job["merged_host"].numpy())
+                seg.mask_dev = None
+                result["segmentation"] = seg._img
             else:
-                # channel order of combine_segmentations (present labels first) applied on the device
-                pres = present.cpu().numpy().astype(bool)
-                perm, names, colors = [], dict(), dict()
+                perm = [int(v) for v in job["perm_host"].numpy()]
+                label_of, color_of = dict(), dict()
                 for k, id in enumerate(ids):
                     m = self.models[id]
-                    p = pres[offs[k]:offs[k + 1]]
                     lab = m.label_names
                     col = m.get_colors() or {}
-                    order = [c for c in range(len(lab)) if p[c]] + [c for c in range(len(lab)) if not p[c]]
-                    for c in order:
-                        names[len(perm) + 1] = lab[c]
+                    for c in range(len(lab)):
+                        label_of[int(offs[k]) + c] = lab[c]
                         if col.get(lab[c]) is not None:
-                            colors[lab[c]] = col[lab[c]]
-                        perm.append(int(offs[k]) + c)
-                merged = ops.permute_channels(mask, perm).cpu().numpy()
+                            color_of[lab[c]] = col[lab[c]]
+                names = dict((j + 1, label_of[c]) for j, c in enumerate(perm))
+                colors = dict((n, color_of[n]) for n in names.values() if n in color_of)
                 minput, input2d, native_2d = model_inputs[ids[0]]
-                seg = Image(merged, input2d.GetSpacing(), input2d.GetOrigin(), input2d.GetDirection(), is_vector=True)
+                seg = Image(job["merged_host"].numpy(), input2d.GetSpacing(), input2d.GetOrigin(), input2d.GetDirection(), is_vector=True)
                 set_annotation_meta(seg, names=names, colors=colors)
                 result["segmentation"] = seg if collapse or native_2d else self._restore_dimension(seg, minput)
 
