@@ -274,21 +274,13 @@ def barrier(world):
 
 
 def max_over_ranks(x: float, world) -> float:
-    if world == 1:
-        return x
-    import torch.distributed as dist
-    t = torch.tensor([x], dtype=torch.float64, device="cuda")
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    return float(t.item())
+    from totalsegmentator2d_b200 import shard
+    return shard.reduce_max(x)
 
 
 def sum_over_ranks(x: float, world) -> float:
-    if world == 1:
-        return x
-    import torch.distributed as dist
-    t = torch.tensor([x], dtype=torch.float64, device="cuda")
-    dist.all_reduce(t, op=dist.ReduceOp.SUM)
-    return float(t.item())
+    from totalsegmentator2d_b200 import shard
+    return shard.reduce_sum(x)
 
 
 def run_b200(args):
@@ -310,8 +302,9 @@ def run_b200(args):
 
     # synthetic studies: S distinct volumes per rank, pinned on the host and resident in HBM
     host_vols = []
-    for i in range(S):
-        v = torch.from_numpy(synthetic_volume(20260000 + rank * S + i, shape)).pin_memory()
+    from totalsegmentator2d_b200 import shard
+    for i in shard.shard_indices(S * world, rank, world):      # study i -> rank i mod world
+        v = torch.from_numpy(synthetic_volume(20260000 + i, shape)).pin_memory()
         host_vols.append(v)
     dev_vols = [v.cuda(non_blocking=True) for v in host_vols]
     H, W = shape[0], shape[2]

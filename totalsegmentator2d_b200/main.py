@@ -41,13 +41,20 @@ def ts2d_run(src: str, dest: str, model: str = None, use_remote: bool = True, fe
         "This is the B200-native implementation of the TS2D inference path; please cite the TS2D paper when using it:\n"
         "Sabrowsky-Hirsch, B., Alshenoudy, A., Thumfart, S., & Giretzlehner, M. (2025). TotalSegmentator 2D: A Tool for Rapid "
         f"Anatomical Structure Analysis. MIUA 2025, pp. 32-43.\n{bar}\n")
+    from . import shard
+    rank, world, local = shard.rank_world()
+    if world > 1:      # launched under torchrun: one process per GPU, cases sharded round robin, no collective on the data path
+        import torch
+        torch.cuda.set_device(local)
     with TS2D(key=model, use_remote=use_remote, fetch_remote=fetch_remote) as ts:
-        cases = list(_enumerate_cases(src))
+        all_cases = list(_enumerate_cases(src))
+        cases = shard.shard(all_cases, rank, world)
         n_cases = len(cases)
-        log(f"Predicting {n_cases} case{'s' if n_cases != 1 else ''}")
-        for case_id, (name, path) in enumerate(cases):
-            log(f"[{case_id + 1}/{n_cases}] Processing: {name}")
-            res = ts.predict(path, collapse=collapse)
+        log(f"Predicting {n_cases} case{'s' if n_cases != 1 else ''}" + (f" (rank {rank} of {world}, {len(all_cases)} in total)" if world > 1 else ""))
+        # pipelined: while case i computes, case i+1 is uploaded and case i-1 is downloaded and written
+        results = ts.predict_batch((path for _, path in cases), collapse=collapse)
+        for case_id, ((name, path), res) in enumerate(zip(cases, results)):
+            log(f"[{case_id + 1}/{n_cases}] Processed: {name}")
             res.save(dest=dest, name=name, models=models, content=content, targets=["segmentation", "projection"])
 
 
