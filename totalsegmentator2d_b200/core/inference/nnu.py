@@ -172,9 +172,12 @@ class NNUDeviceModel(NNUModel):
         return seg
 
     def predict_device(self, img_dev: torch.Tensor, spacing_xy, mask: Optional[torch.Tensor] = None, ch_off: int = 0,
-                       present: Optional[torch.Tensor] = None, cache: Optional[dict] = None, cache_key=()) -> torch.Tensor:
+                       present: Optional[torch.Tensor] = None, cache: Optional[dict] = None, cache_key=(),
+                       prepare_only: bool = False) -> torch.Tensor:
         """(C, H, W) float32 CUDA image -> uint8 mask [H][W][ch_total] on the device (this model's channel window).
-        Stage order = reference prediction_worker.py:194-221: preprocess -> predict -> export."""
+        Stage order = reference prediction_worker.py:194-221: preprocess -> predict -> export.
+        ``prepare_only`` stops after preprocessing + tiling (fills ``cache``): the caller then runs the models on
+        separate streams."""
         p = self.predictor
         C, H, W = img_dev.shape
         if mask is None:
@@ -187,6 +190,8 @@ class NNUDeviceModel(NNUModel):
             entry = (data.shape, props, x, layout)
             if cache is not None:
                 cache[key] = entry
+        if prepare_only:
+            return mask
         shape, props, x, layout = entry
         (_, (h0, h1), (w0, w1)) = props["bbox_used_for_cropping"]
         hw = (int(shape[1]), int(shape[2]))

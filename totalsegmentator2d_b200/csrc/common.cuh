@@ -70,6 +70,13 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
+// 16-byte streaming load (read once: do not allocate in L1)
+__device__ __forceinline__ uint4 ld_stream_16(const void *p) {
+    uint4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
+
 // sliding-window tile origins (y, x) in padded coordinates, passed by value in kernel-parameter space
 constexpr int kMaxTiles = 1024;
 template <int CAP> struct TileListT { int T; int yx[CAP][2]; };

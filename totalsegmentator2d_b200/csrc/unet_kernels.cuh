@@ -220,6 +220,45 @@ __global__ void __launch_bounds__(256) norm_act_kernel(const T *raw, const doubl
     const T *src = raw + ((long long)n * HW) * C;
     T *dst = out + ((long long)n * HW) * out_ps;
     if constexpr (sizeof(T) == 2) {
+        if ((C & 7) == 0 && (out_ps & 7) == 0 && (256 % (C >> 3)) == 0) {
+            // a thread keeps ONE block of 8 channels (256 is a multiple of C/8): scale / shift live in registers, the pixel
+            // index advances by a constant, and 4 independent 16-byte loads are in flight per thread (no divisions in the loop)
+            const int cv = C >> 3;
+            const int cb = threadIdx.x % cv, pstep = 256 / cv;
+            float sc[8], sh[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { sc[j] = s_ss[cb * 8 + j]; sh[j] = s_ss[C + cb * 8 + j]; }
+            long long pix = p0 + threadIdx.x / cv;
+            const T *s = src + pix * C + cb * 8;
+            T *d = dst + pix * out_ps + cb * 8;
+            const long long s_step = (long long)pstep * C, d_step = (long long)pstep * out_ps;
+            auto apply = [&](uint4 &v) {
+                uint32_t *w = reinterpret_cast<uint32_t *>(&v);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float2 f = unpack2<T>(w[k]);
+                    float y0 = fmaf(f.x, sc[2 * k], sh[2 * k]), y1 = fmaf(f.y, sc[2 * k + 1], sh[2 * k + 1]);
+                    y0 = y0 > 0.f ? y0 : y0 * slope;
+                    y1 = y1 > 0.f ? y1 : y1 * slope;
+                    w[k] = pack2<T>(y0, y1);
+                }
+            };
+            for (; pix + 3 * pstep < p1; pix += 4 * pstep, s += 4 * s_step, d += 4 * d_step) {
+                uint4 v[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) v[u] = ld_stream_16(s + u * s_step);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) apply(v[u]);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) *reinterpret_cast<uint4 *>(d + u * d_step) = v[u];
+            }
+            for (; pix < p1; pix += pstep, s += s_step, d += d_step) {
+                uint4 v = ld_stream_16(s);
+                apply(v);
+                *reinterpret_cast<uint4 *>(d) = v;
+            }
+            return;
+        }
         if ((C & 7) == 0 && (out_ps & 7) == 0) {
             const int cv = C >> 3;
             for (long long i = p0 * cv + threadIdx.x; i < p1 * cv; i += blockDim.x) {

@@ -64,6 +64,7 @@ class TS2D:
         colors = get_label_colors()
         p = {"server.workers": 1, "nnu.result.colors": colors}
         p.update(param or {})
+        self._param = dict(p)
         L.load(check_device=True)       # fail loudly: no CPU fallback
         self.zoo = NNUZoo(remote=False, root=models_root)
         self.models: Dict[str, NNUDeviceModel] = dict()
@@ -137,13 +138,52 @@ class TS2D:
         else:
             present.zero_()
         cache = dict()
-        for k, id in enumerate(ids):
-            try:
-                key = (imgs_dev[id].data_ptr(),)
-                self.models[id].predict_device(imgs_dev[id], spacing_xy, mask=mask, ch_off=offs[k], present=present, cache=cache, cache_key=key)
-            except L.TS2DError as ex:
-                raise RuntimeError(f"Prediction failed for: {id} ({ex})") from ex
+        side = self._model_streams(len(ids))
+        try:
+            if not side:
+                for k, id in enumerate(ids):
+                    key = (imgs_dev[id].data_ptr(),)
+                    self.models[id].predict_device(imgs_dev[id], spacing_xy, mask=mask, ch_off=offs[k], present=present, cache=cache, cache_key=key)
+            else:
+                # the group models of one study are independent (reference tool.py:110-112 loops over them): preprocess and
+                # tile once on the caller's stream, then fan the U-Nets out over side streams so that the latency-bound
+                # low-resolution layers of one model fill the SMs the other models leave idle; join before returning
+                # (every tensor the side streams touch is still referenced here, so the caching allocator cannot recycle it)
+                cur = torch.cuda.current_stream()
+                for k, id in enumerate(ids):
+                    key = (imgs_dev[id].data_ptr(),)
+                    self.models[id].predict_device(imgs_dev[id], spacing_xy, mask=mask, ch_off=offs[k], present=present, cache=cache,
+                                                   cache_key=key, prepare_only=True)
+                fork = torch.cuda.Event()
+                fork.record(cur)
+                joins = []
+                for k, id in enumerate(ids):
+                    s = side[k % len(side)]
+                    if k < len(side):
+                        s.wait_event(fork)
+                    with torch.cuda.stream(s):
+                        key = (imgs_dev[id].data_ptr(),)
+                        self.models[id].predict_device(imgs_dev[id], spacing_xy, mask=mask, ch_off=offs[k], present=present, cache=cache,
+                                                       cache_key=key)
+                for s in side[:len(ids)]:
+                    ev = torch.cuda.Event()
+                    ev.record(s)
+                    cur.wait_event(ev)
+        except L.TS2DError as ex:
+            raise RuntimeError(f"Prediction failed for: {id} ({ex})") from ex
         return {"mask": mask, "present": present, "offsets": offs}
+
+    def _model_streams(self, n_models: int):
+        """side streams the group models of one study are spread over (``b200.model_streams`` / $TS2D_MODEL_STREAMS;
+        0 or 1 = everything on the caller's stream)."""
+        want = int(os.environ.get("TS2D_MODEL_STREAMS", self._param.get("b200.model_streams", 3)))
+        want = min(want, n_models)
+        if want <= 1:
+            return []
+        pool = getattr(self, "_side_streams", None)
+        if pool is None or len(pool) != want:
+            pool = self._side_streams = [torch.cuda.Stream() for _ in range(want)]
+        return pool
 
     def predict_volume_device(self, vol_dev: torch.Tensor, spacing_xyz, direction=None, mask: Optional[torch.Tensor] = None,
                               present: Optional[torch.Tensor] = None) -> dict:
