@@ -312,9 +312,16 @@ def run_b200(args):
     presents = [torch.zeros(n_heads, dtype=torch.uint8, device="cuda") for _ in range(S)]
     torch.cuda.synchronize()
 
+    from totalsegmentator2d_b200 import ops as _ops
+    merged = [torch.empty_like(m) for m in masks]
+    offs = ts.head_offsets()
+
     def step_device():
+        # one study = projection -> preprocess -> 5 group U-Nets -> blend / threshold -> merged 117-channel mask in the
+        # reference's channel order (combine_segmentations), everything resident in HBM
         for i in range(S):
             ts.predict_volume_device(dev_vols[i], SPACING, None, mask=masks[i], present=presents[i])
+            _ops.merge_present_order(masks[i], presents[i], offs, out=merged[i])
 
     def launches_now():
         return int(lib.ts2d_launch_count())
@@ -345,8 +352,16 @@ def run_b200(args):
     preds = [ts.models[m].predictor for m in ts.models]
     for p in preds:
         p.set_profiling(True)
+    # the per-launch CUDA events only mean something when the launches do not overlap: this pass runs the five group
+    # models back to back on ONE stream (the timed region above spreads them over side streams)
+    prev_streams = os.environ.get("TS2D_MODEL_STREAMS")
+    os.environ["TS2D_MODEL_STREAMS"] = "1"
     ts.predict_volume_device(dev_vols[0], SPACING, None, mask=masks[0], present=presents[0])
     torch.cuda.synchronize()
+    if prev_streams is None:
+        del os.environ["TS2D_MODEL_STREAMS"]
+    else:
+        os.environ["TS2D_MODEL_STREAMS"] = prev_streams
     conv_ms = sum(p.last_conv_ms() for p in preds)
     for p in preds:
         p.set_profiling(False)
@@ -408,6 +423,17 @@ def run_b200(args):
         cpu = {"value": 1.0 / s["study_seconds"], "unit": UNIT, "cores": ref.cores, "kind": "port", "sample": ref.describe(shape),
                "stage_seconds": {k: s[k] for k in ("projected", "preprocessed", "tile_predicted", "exported")}}
 
+    # DRAM bytes of the conv launches measured by ncu --set full (tools/ncu_summary.py -> profiles/ncu_traffic.json),
+    # scaled from the captured forward (batch of tiles x mirrors of ONE model) to one study (all group models)
+    conv_traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            tj = json.load(f)
+        if not args.small and tj.get("batch") == tiles_per_model * M:
+            conv_traffic = float(tj["conv_dram_bytes_per_forward"]) * len(preds)
+    except Exception:
+        conv_traffic = None
+
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
                 "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -415,7 +441,9 @@ def run_b200(args):
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
                 "roofline": {"bound": "tensor", "kernel": "conv_tc_kernel (tcgen05 implicit-GEMM conv, all conv/transposed-conv launches of one study)",
                              "achieved": conv_tflops, "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
-                             "frac": conv_tflops / peaks["bf16_tflops_sustained"], "traffic": None, "peak_source": peak_src + " (sustained)",
+                             "frac": conv_tflops / peaks["bf16_tflops_sustained"], "traffic": conv_traffic,
+                             "traffic_note": "DRAM read+write bytes of the conv launches of one study (ncu --set full, profiles/ncu_traffic.json); the step is one study's launches, so achieved/traffic are per study",
+                             "peak_source": peak_src + " (sustained)",
                              "conv_ms_per_study": conv_ms, "conv_flops_per_study": conv_flops},
                 "roofline_hbm": {"bound": "hbm", "kernel": "project_strided_i16_kernel", "achieved": proj_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                                  "frac": proj_gbs / peaks["hbm_gbs"], "traffic": None, "peak_source": peak_src, "ms": proj_ms, "bytes": proj_bytes},

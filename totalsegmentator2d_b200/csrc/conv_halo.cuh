@@ -30,7 +30,7 @@
 // are latency bound when left to one warp per scheduler:
 //   transform (FUSE)  all 256 worker threads rewrite the halo of tile j (16-byte chunks, loads batched before math);
 //   epilogue          TMEM -> +bias -> round -> per-thread InstanceNorm partial sums -> 32-byte global stores, for
-//                     tile j - kLag.  BN == 32: the two worker warpgroups alternate tiles (group g owns TMEM buffer
+//                     tile j - kLag (statistics from the fp32 values, FADD2 / FFMA2: see epi_chunk).  BN == 32: the two worker warpgroups alternate tiles (group g owns TMEM buffer
 //                     g); BN == 64: both work on every tile, one half of the columns each.
 #pragma once
 #include "conv_tc.cuh"
@@ -212,16 +212,12 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // InstanceNorm statistics: every thread keeps running sums of ITS pixel row for its 32 channels across the tiles of
         // one image (no cross-lane traffic per tile); the 32-lane transpose-reduction and the double atomics happen only
         // when the image changes (<= 3 flushes per CTA with the contiguous partition).
-        float tacc1[32], tacc2[32];
+        uint64_t tacc1[16], tacc2[16];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) { tacc1[i] = 0.f; tacc2[i] = 0.f; }
+        for (int i = 0; i < 16; ++i) { tacc1[i] = 0ull; tacc2[i] = 0ull; }
         auto flush_stats = [&](int n_img) {
-            float b[32];
-#pragma unroll
-            for (int j = 0; j < 32; ++j) b[j] = tacc2[j];
-            const float s1 = warp_transpose_sum32(tacc1, lane), s2 = warp_transpose_sum32(b, lane);
-#pragma unroll
-            for (int j = 0; j < 32; ++j) { tacc1[j] = 0.f; tacc2[j] = 0.f; }
+            float s1, s2;
+            epi_flush(tacc1, tacc2, lane, s1, s2);
             double *s = p.stats + ((long long)n_img * p.Cout + nt * BN + col0 + lane) * 2;
             atomicAdd(s, (double)s1);
             atomicAdd(s + 1, (double)s2);
@@ -351,28 +347,13 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             tcgen05_fence_before();
             mbar_arrive(&tmem_empty[buf]);        // this thread's TMEM reads of the tile are done
             uint32_t pk[16];
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                const float4 b = *reinterpret_cast<const float4 *>(&s_bias[col0 + 4 * k]);     // warp-uniform address: broadcast
-                pk[2 * k] = pack2<DT>(__uint_as_float(r[4 * k]) + b.x, __uint_as_float(r[4 * k + 1]) + b.y);
-                pk[2 * k + 1] = pack2<DT>(__uint_as_float(r[4 * k + 2]) + b.z, __uint_as_float(r[4 * k + 3]) + b.w);
-            }
+            epi_chunk<DT>(r, s_bias + col0, pk, tacc1, tacc2, do_stats && valid);
             if (valid) {
                 // 2 x 32-byte stores (STG.256): every sector is written whole by one instruction
 #pragma unroll
                 for (int k = 0; k < 2; ++k)
                     asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst + 16 * k), "r"(pk[8 * k]), "r"(pk[8 * k + 1]),
                                  "r"(pk[8 * k + 2]), "r"(pk[8 * k + 3]), "r"(pk[8 * k + 4]), "r"(pk[8 * k + 5]), "r"(pk[8 * k + 6]), "r"(pk[8 * k + 7]) : "memory");
-                if (do_stats) {
-#pragma unroll
-                    for (int k = 0; k < 16; ++k) {
-                        const float2 f = unpack2<DT>(pk[k]);          // statistics of the ROUNDED values (what the consumer normalises)
-                        tacc1[2 * k] += f.x;
-                        tacc1[2 * k + 1] += f.y;
-                        tacc2[2 * k] = fmaf(f.x, f.x, tacc2[2 * k]);
-                        tacc2[2 * k + 1] = fmaf(f.y, f.y, tacc2[2 * k + 1]);
-                    }
-                }
             }
             tx += esx; if (tx >= p.tiles_x) { tx -= p.tiles_x; ++ty; }
             ty += esy; if (ty >= p.tiles_y) { ty -= p.tiles_y; ++n; }

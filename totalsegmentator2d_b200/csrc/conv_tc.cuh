@@ -188,6 +188,69 @@ template <typename DT> __device__ __forceinline__ float2 unpack2(uint32_t u);
 template <> __device__ __forceinline__ float2 unpack2<__nv_bfloat16>(uint32_t u) { return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162 *>(&u)); }
 template <> __device__ __forceinline__ float2 unpack2<__half>(uint32_t u) { return __half22float2(*reinterpret_cast<__half2 *>(&u)); }
 
+// ---- packed fp32x2 arithmetic (FADD2 / FFMA2 on sm_100): two lanes per issue slot in the epilogues ----
+__device__ __forceinline__ uint64_t f32x2_pack(float lo, float hi) { uint64_t r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ uint64_t f32x2_pack_bits(uint32_t lo, uint32_t hi) { uint64_t r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo), "r"(hi)); return r; }
+__device__ __forceinline__ float f32x2_lo(uint64_t v) { return __uint_as_float((uint32_t)v); }
+__device__ __forceinline__ float f32x2_hi(uint64_t v) { return __uint_as_float((uint32_t)(v >> 32)); }
+__device__ __forceinline__ uint64_t f32x2_add(uint64_t a, uint64_t b) { uint64_t r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ uint64_t f32x2_mul(uint64_t a, uint64_t b) { uint64_t r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ uint64_t f32x2_fma(uint64_t a, uint64_t b, uint64_t c) { uint64_t r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+
+// One 32-column accumulator chunk of a thread's pixel row: v = acc + bias (fp32x2), pk = v rounded to DT (what is stored),
+// and - when `stats` - the thread's running InstanceNorm sums t1 += v, t2 += v*v.  The statistics are taken from the fp32
+// values BEFORE rounding: that is what InstanceNorm sees in the fp32 reference, and it saves the unpack of the rounded pairs
+// (the epilogue is issue-slot bound: 64 instructions per chunk instead of 144).  bias32: 32 floats, 16-byte aligned, or null.
+template <typename DT>
+__device__ __forceinline__ void epi_chunk(const uint32_t (&r)[32], const float *bias32, uint32_t (&pk)[16], uint64_t (&t1)[16], uint64_t (&t2)[16],
+                                          bool stats) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        uint64_t v0 = f32x2_pack_bits(r[4 * k], r[4 * k + 1]), v1 = f32x2_pack_bits(r[4 * k + 2], r[4 * k + 3]);
+        if (bias32) {
+            const float4 b = *reinterpret_cast<const float4 *>(bias32 + 4 * k);       // warp-uniform address: broadcast
+            v0 = f32x2_add(v0, f32x2_pack(b.x, b.y));
+            v1 = f32x2_add(v1, f32x2_pack(b.z, b.w));
+        }
+        pk[2 * k] = pack2<DT>(f32x2_lo(v0), f32x2_hi(v0));
+        pk[2 * k + 1] = pack2<DT>(f32x2_lo(v1), f32x2_hi(v1));
+        if (stats) {
+            t1[2 * k] = f32x2_add(t1[2 * k], v0);
+            t1[2 * k + 1] = f32x2_add(t1[2 * k + 1], v1);
+            t2[2 * k] = f32x2_fma(v0, v0, t2[2 * k]);
+            t2[2 * k + 1] = f32x2_fma(v1, v1, t2[2 * k + 1]);
+        }
+    }
+}
+// same without accumulation: v[16] = the 32 fp32 values (acc + bias) as pairs
+template <typename DT>
+__device__ __forceinline__ void epi_vals(const uint32_t (&r)[32], const float *bias32, uint32_t (&pk)[16], uint64_t (&v)[16]) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        uint64_t v0 = f32x2_pack_bits(r[4 * k], r[4 * k + 1]), v1 = f32x2_pack_bits(r[4 * k + 2], r[4 * k + 3]);
+        if (bias32) {
+            const float4 b = *reinterpret_cast<const float4 *>(bias32 + 4 * k);
+            v0 = f32x2_add(v0, f32x2_pack(b.x, b.y));
+            v1 = f32x2_add(v1, f32x2_pack(b.z, b.w));
+        }
+        pk[2 * k] = pack2<DT>(f32x2_lo(v0), f32x2_hi(v0));
+        pk[2 * k + 1] = pack2<DT>(f32x2_lo(v1), f32x2_hi(v1));
+        v[2 * k] = v0;
+        v[2 * k + 1] = v1;
+    }
+}
+// per-thread fp32x2 sums -> lane L gets the warp total of channel L (and the accumulators are cleared)
+__device__ __forceinline__ float warp_transpose_sum32(float (&x)[32], int lane);
+__device__ __forceinline__ void epi_flush(uint64_t (&t1)[16], uint64_t (&t2)[16], int lane, float &s1, float &s2) {
+    float a[32];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) { a[2 * j] = f32x2_lo(t1[j]); a[2 * j + 1] = f32x2_hi(t1[j]); t1[j] = 0ull; }
+    s1 = warp_transpose_sum32(a, lane);
+#pragma unroll
+    for (int j = 0; j < 16; ++j) { a[2 * j] = f32x2_lo(t2[j]); a[2 * j + 1] = f32x2_hi(t2[j]); t2[j] = 0ull; }
+    s2 = warp_transpose_sum32(a, lane);
+}
+
 // lane L ends up with the sum over the warp of x[L]; 31 shuffles
 __device__ __forceinline__ float warp_transpose_sum32(float (&x)[32], int lane) {
 #pragma unroll
@@ -317,22 +380,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         DT *out = reinterpret_cast<DT *>(p.out);
         const bool do_stats = p.stats != nullptr;
         const bool fast_stats = do_stats && p.tn == 1;     // a tile lies inside one image: sums can stay in registers across tiles
-        float tacc1[kThreadAcc ? 32 : 1], tacc2[kThreadAcc ? 32 : 1];     // per-thread sums of this thread's pixel row (kThreadAcc)
+        uint64_t tacc1[16], tacc2[16];                                    // per-thread fp32x2 sums of this thread's pixel row (kThreadAcc)
         float racc1[kMyChunks], racc2[kMyChunks];                         // per-lane (= per-channel) sums (otherwise)
 #pragma unroll
-        for (int i = 0; i < (kThreadAcc ? 32 : 1); ++i) { tacc1[i] = 0.f; tacc2[i] = 0.f; }
+        for (int i = 0; i < 16; ++i) { tacc1[i] = 0ull; tacc2[i] = 0ull; }
 #pragma unroll
         for (int i = 0; i < kMyChunks; ++i) { racc1[i] = 0.f; racc2[i] = 0.f; }
         auto flush_stats = [&](int n_img, int nt_blk) {
-            if constexpr (kThreadAcc) {
-                float b[32];
-#pragma unroll
-                for (int j = 0; j < 32; ++j) b[j] = tacc2[j];
-                racc1[0] = warp_transpose_sum32(tacc1, lane);
-                racc2[0] = warp_transpose_sum32(b, lane);
-#pragma unroll
-                for (int j = 0; j < 32; ++j) { tacc1[j] = 0.f; tacc2[j] = 0.f; }
-            }
+            if constexpr (kThreadAcc) epi_flush(tacc1, tacc2, lane, racc1[0], racc2[0]);
 #pragma unroll
             for (int c = 0; c < kMyChunks; ++c) {
                 double *s = p.stats + ((long long)n_img * p.Cout + nt_blk * BN + (chunk0 + c) * 32 + lane) * 2;
@@ -382,13 +437,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 const int dy = tap / p.mx, dx = tap - dy * p.mx;
                 DT *dst = opix + ((long long)dy * p.Wfull + dx) * p.out_ps + c0;
                 uint32_t pk[16];
-#pragma unroll
-                for (int k = 0; k < 8; ++k) {
-                    float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (p.bias) b = __ldg(reinterpret_cast<const float4 *>(p.bias + c0) + k);      // warp-uniform address
-                    pk[2 * k] = pack2<DT>(__uint_as_float(r[4 * k]) + b.x, __uint_as_float(r[4 * k + 1]) + b.y);
-                    pk[2 * k + 1] = pack2<DT>(__uint_as_float(r[4 * k + 2]) + b.z, __uint_as_float(r[4 * k + 3]) + b.w);
-                }
+                uint64_t v[16];                  // fp32 values of this chunk (warp-reduced path only)
+                const bool tstat = do_stats && kThreadAcc && fast_stats;
+                if (tstat) epi_chunk<DT>(r, p.bias ? p.bias + c0 : nullptr, pk, tacc1, tacc2, valid);     // overhanging rows do not contribute
+                else epi_vals<DT>(r, p.bias ? p.bias + c0 : nullptr, pk, v);
                 if (valid) {
                     // 2 x 32-byte stores (STG.256): every sector is written whole by one instruction
 #pragma unroll
@@ -396,40 +448,25 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst + 16 * k), "r"(pk[8 * k]), "r"(pk[8 * k + 1]),
                                      "r"(pk[8 * k + 2]), "r"(pk[8 * k + 3]), "r"(pk[8 * k + 4]), "r"(pk[8 * k + 5]), "r"(pk[8 * k + 6]), "r"(pk[8 * k + 7]) : "memory");
                 }
-                if (do_stats) {
-                    // statistics of the ROUNDED values (what the consumer normalises)
-                    if (kThreadAcc && fast_stats) {
-                        if (valid) {
+                if (do_stats && !tstat) {
+                    float a[32], b[32];
 #pragma unroll
-                            for (int k = 0; k < 16; ++k) {
-                                const float2 f = unpack2<DT>(pk[k]);
-                                tacc1[2 * k] += f.x;
-                                tacc1[2 * k + 1] += f.y;
-                                tacc2[2 * k] = fmaf(f.x, f.x, tacc2[2 * k]);
-                                tacc2[2 * k + 1] = fmaf(f.y, f.y, tacc2[2 * k + 1]);
-                            }
-                        }
-                    } else {
-                        float a[32], b[32];
+                    for (int k = 0; k < 16; ++k) {
+                        a[2 * k] = valid ? f32x2_lo(v[k]) : 0.f;
+                        a[2 * k + 1] = valid ? f32x2_hi(v[k]) : 0.f;
+                    }
 #pragma unroll
-                        for (int k = 0; k < 16; ++k) {
-                            const float2 f = unpack2<DT>(pk[k]);
-                            a[2 * k] = valid ? f.x : 0.f;
-                            a[2 * k + 1] = valid ? f.y : 0.f;
-                        }
-                        if (fast_stats) {
+                    for (int k = 0; k < 32; ++k) b[k] = a[k] * a[k];
+                    if (fast_stats) {
+                        racc1[c] += warp_transpose_sum32(a, lane);
+                        racc2[c] += warp_transpose_sum32(b, lane);
+                    } else if (valid) {
+                        // several images per tile (tiny levels): one atomic pair per value
+                        double *s = p.stats + ((long long)n * p.Cout + gcol) * 2;
 #pragma unroll
-                            for (int k = 0; k < 32; ++k) b[k] = a[k] * a[k];
-                            racc1[c] += warp_transpose_sum32(a, lane);
-                            racc2[c] += warp_transpose_sum32(b, lane);
-                        } else if (valid) {
-                            // several images per tile (tiny levels): one atomic pair per value
-                            double *s = p.stats + ((long long)n * p.Cout + gcol) * 2;
-#pragma unroll
-                            for (int k = 0; k < 32; ++k) {
-                                atomicAdd(s + 2 * k, (double)a[k]);
-                                atomicAdd(s + 2 * k + 1, (double)a[k] * (double)a[k]);
-                            }
+                        for (int k = 0; k < 32; ++k) {
+                            atomicAdd(s + 2 * k, (double)a[k]);
+                            atomicAdd(s + 2 * k + 1, (double)b[k]);
                         }
                     }
                 }

@@ -18,6 +18,7 @@
 
 #include "conv_tc.cuh"
 #include "conv_halo.cuh"
+#include "conv_first_tc.cuh"
 #include "unet_kernels.cuh"
 
 namespace ts2d {
@@ -61,6 +62,7 @@ struct ConvLayer {
     bool halo = false;          // conv_halo_kernel (3x3 stride 1, halo tile + resident weights)
     int halo_bn = 0, halo_stages = 0;
     bool halo_maps = false;
+    bool first_tc = false;      // conv_first_tc_kernel (CIN == 2, 3x3 stride 1: im2col rows built by the workers, K = 32)
     bool first_fast = false;    // conv_first_kernel (CIN <= 4, 3x3 stride 1, 16-bit activations)
     void *out_raw = nullptr;    // pre-normalisation output (ping-pong between two buffers)
     bool defer = false;         // no norm_act pass: the consumer applies InstanceNorm + LeakyReLU on its operand path
@@ -288,6 +290,25 @@ static int launch_first(int cin, const FirstConvParams &p, int N, cudaStream_t s
     TS2D_LAUNCH_CHECK();
     return TS2D_OK;
 }
+template <typename DT>
+static int launch_first_tc(const FirstTcParams &p, cudaStream_t st) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        TS2D_CHECK_CUDA(cudaFuncSetAttribute(conv_first_tc_kernel<DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFtcSmemBytes));
+        attr_set = true;
+    }
+    const long long total = (long long)p.tiles_x * p.tiles_y * p.N;
+    const int gx = (int)std::max(1LL, std::min(total / 2, (long long)kNumSMs * 2));
+    conv_first_tc_kernel<DT><<<dim3(gx, p.Cout / 32), kFtcThreads, kFtcSmemBytes, st>>>(p);
+    TS2D_LAUNCH_CHECK();
+    return TS2D_OK;
+}
+// tensor-core first conv (conv_first_tc_kernel): two 16-bit input channels, output channels in blocks of 32
+static bool first_tc_eligible(const ts2d_unet_plan &pl, const ConvLayer &c) {
+    static const int enable = getenv("TS2D_FIRST_TC") ? atoi(getenv("TS2D_FIRST_TC")) : 1;
+    return enable && pl.use_tensor_cores && pl.precision != TS2D_PREC_F32 && c.kh == 3 && c.kw == 3 && c.sh == 1 && c.sw == 1 && c.cin == 2 &&
+           c.cout % 32 == 0 && c.in_ps == c.cin;
+}
 static bool first_fast_eligible(const ts2d_unet_plan &pl, const ConvLayer &c) {
     return pl.use_tensor_cores && pl.precision != TS2D_PREC_F32 && c.kh == 3 && c.kw == 3 && c.sh == 1 && c.sw == 1 && c.cin <= 4 &&
            (c.cout == 16 || c.cout == 32 || c.cout == 64) && c.in_ps == c.cin;
@@ -302,8 +323,8 @@ static int launch_direct_any(int precision, const DirectConvParams &p, int N, cu
 template <typename T>
 static int launch_norm(const void *raw, const double *stats, const float *g, const float *b, void *out, long long out_ps, int HW, int C, float eps,
                        float slope, int N, cudaStream_t st) {
+    // <= 4 blocks per SM in total: the whole grid is resident at once (no second partial wave)
     int ppb = std::max(32, ceil_div(HW, std::max(1, (kNumSMs * 4) / std::max(1, N))));
-    ppb = std::min(ppb, 4096);
     dim3 grid(ceil_div(HW, ppb), N);
     norm_act_kernel<T><<<grid, 256, 2 * C * sizeof(float), st>>>((const T *)raw, stats, g, b, (T *)out, out_ps, HW, C, eps, slope, ppb);
     TS2D_LAUNCH_CHECK();
@@ -579,7 +600,8 @@ extern "C" int ts2d_unet_finalize(ts2d_unet *u) {
         c.enc_n = 0;
         c.halo = halo_config(c, c.halo_bn, c.halo_stages);
         c.halo_maps = false;
-        c.first_fast = !c.tc && first_fast_eligible(pl, c);
+        c.first_tc = !c.tc && first_tc_eligible(pl, c);
+        c.first_fast = !c.tc && !c.first_tc && first_fast_eligible(pl, c);
         c.defer = false; c.prod = -1;
     }
     // ---- deferred normalisation: producer writes raw + statistics only, the consumer normalises while loading ----
@@ -704,6 +726,13 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
             c.enc_n = N;
         }
         rc = is_bf16 ? launch_tc<__nv_bfloat16>(bn, c.kc, c.tmA, c.tmB, p, st) : launch_tc<__half>(bn, c.kc, c.tmA, c.tmB, p, st);
+        if (rc) return rc;
+    } else if (c.first_tc) {
+        FirstTcParams p;
+        memset(&p, 0, sizeof(p));
+        p.in = c.in; p.N = N; p.H = c.Hin; p.W = c.Win; p.w = c.w_direct; p.bias = c.b.dev; p.out = c.out_raw; p.Cout = c.cout; p.stats = c.stats;
+        p.tiles_x = ceil_div(c.Wout, 8); p.tiles_y = ceil_div(c.Hout, 16);
+        rc = is_bf16 ? launch_first_tc<__nv_bfloat16>(p, st) : launch_first_tc<__half>(p, st);
         if (rc) return rc;
     } else if (c.first_fast) {
         FirstConvParams p;
@@ -878,7 +907,7 @@ template <typename T, int CAP>
 static int launch_blend(const BlendParams &p, const int *tile_yx_host, int F, cudaStream_t st) {
     const long long npix = (long long)p.h * p.w;
     const int grid = ceil_div(npix, 128);
-    const size_t smem = (size_t)(p.heads * F + p.heads) * sizeof(float) + (size_t)128 * p.heads;
+    const size_t smem = (size_t)(p.heads * F + p.heads) * sizeof(float) + (size_t)128 * p.heads + 16 + 128 * sizeof(long long) + (size_t)p.heads * sizeof(int);
     TileListT<CAP> tl;
     fill_tile_list(tl, tile_yx_host, p.T);
     switch (F) {

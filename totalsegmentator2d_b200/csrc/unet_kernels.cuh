@@ -286,7 +286,7 @@ __global__ void __launch_bounds__(256) norm_act_kernel(const T *raw, const doubl
     }
 }
 
-// scale / shift of InstanceNorm per (image, channel) from the epilogue statistics: ss[(n*C + c)*2] = {scale, shift};
+// scale / shift of InstanceNorm per (image, channel) from the epilogue statistics (C even; pair layout, see below);
 // same arithmetic as norm_act_kernel.  Used when the last decoder conv's normalisation is applied by blend_head_kernel.
 __global__ void __launch_bounds__(256) norm_finalize_kernel(const double *stats, const float *gamma, const float *beta, float *ss, int NC, int C,
                                                             int HW, float eps) {
@@ -297,8 +297,10 @@ __global__ void __launch_bounds__(256) norm_finalize_kernel(const double *stats,
     const double var = fmax(stats[(long long)i * 2 + 1] / (double)HW - mean * mean, 0.0);
     const double rstd = 1.0 / sqrt(var + (double)eps);
     const float g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
-    ss[(long long)i * 2] = (float)(rstd * (double)g);
-    ss[(long long)i * 2 + 1] = (float)((double)b - mean * rstd * (double)g);
+    // layout per channel PAIR: {scale[2j], scale[2j+1], shift[2j], shift[2j+1]} - one 16-byte load gives the two fp32x2 operands
+    float *o = ss + (long long)(i >> 1) * 4 + (i & 1);
+    o[0] = (float)(rstd * (double)g);
+    o[2] = (float)((double)b - mean * rstd * (double)g);
 }
 
 // ------------------------------------------------------------------------------------------------------
@@ -319,13 +321,15 @@ struct BlendParams {
     int W0, h0, w0, ch_off, ch_total;
     uint8_t *present;          // [ch_total] or null
     const float *feat_ss;      // null: feat is normalised + activated; else feat is the raw conv output and {scale, shift}
-    float slope;               //       [T*M][F][2] + LeakyReLU(slope) are applied here (rounded to T like norm_act_kernel does)
+    float slope;               //       (pair layout of norm_finalize_kernel) + LeakyReLU(slope) are applied here in fp32
 };
 
 template <typename T, int F, int CAP>
 __global__ void __launch_bounds__(128) blend_head_kernel(const BlendParams p, const __grid_constant__ TileListT<CAP> tl) {
-    extern __shared__ float s_head[];            // head_w [heads][F], head_b [heads], then the block's mask bytes [128][heads]
+    extern __shared__ __align__(16) float s_head[];            // head_w [heads][F], head_b [heads], then the block's mask bytes [128][heads]
     uint8_t *s_mask = reinterpret_cast<uint8_t *>(s_head + p.heads * F + p.heads);
+    int *s_any = reinterpret_cast<int *>(reinterpret_cast<long long *>(s_head) + ((p.heads * F + p.heads) * 4 + 128 * p.heads + 7) / 8 + 128);   // [heads]
+    for (int i = threadIdx.x; i < p.heads; i += blockDim.x) s_any[i] = 0;
     for (int i = threadIdx.x; i < p.heads * F; i += blockDim.x) s_head[i] = p.head_w[i];
     for (int i = threadIdx.x; i < p.heads; i += blockDim.x) s_head[p.heads * F + i] = p.head_b ? p.head_b[i] : 0.f;
     __syncthreads();
@@ -336,8 +340,13 @@ __global__ void __launch_bounds__(128) blend_head_kernel(const BlendParams p, co
     const int y = active ? (int)(pix / p.w) : 0, x = active ? (int)(pix % p.w) : 0;
     const int yp = y + p.pad_top, xp = x + p.pad_left;
     float acc[F];
+    uint64_t acc2[F / 2];                          // 16-bit fast path: fp32 pairs
 #pragma unroll
     for (int k = 0; k < F; ++k) acc[k] = 0.f;
+#pragma unroll
+    for (int k = 0; k < F / 2; ++k) acc2[k] = 0ull;
+    const uint64_t slope2 = f32x2_pack(p.slope, p.slope);
+    const bool slope01 = p.slope >= 0.f && p.slope <= 1.f;       // LeakyReLU(y) == max(y, slope*y)
     float wsum = 0.f;
     const T *feat = reinterpret_cast<const T *>(p.feat);
     const float inv_m = 1.0f / (float)p.M;
@@ -347,44 +356,63 @@ __global__ void __launch_bounds__(128) blend_head_kernel(const BlendParams p, co
         const float g = p.gauss[ly * p.Pw + lx];
         wsum += g;
         const float gm = g * inv_m;
-        for (int m = 0; m < p.M; ++m) {
-            bool fh = false, fw = false;
-            if (p.mirror_mask == 3) { fh = (m == 1 || m == 3); fw = (m == 2 || m == 3); }
-            else if (p.mirror_mask == 1) fh = (m == 1);
-            else if (p.mirror_mask == 2) fw = (m == 1);
-            const int sy = fh ? p.Ph - 1 - ly : ly, sx = fw ? p.Pw - 1 - lx : lx;
-            const T *f = feat + (((long long)(t * p.M + m) * p.Ph + sy) * p.Pw + sx) * F;
-            if constexpr (sizeof(T) == 2 && (F % 8) == 0) {
-                const float4 *ss = reinterpret_cast<const float4 *>(p.feat_ss) + (long long)(t * p.M + m) * (F / 2);    // {sc, sh, sc, sh}: warp-uniform broadcast loads
+        if constexpr (sizeof(T) == 2 && (F % 8) == 0) {
+            // all mirror variants of this tile are loaded before any arithmetic (F/8 x M independent 16-byte loads in flight);
+            // normalisation, LeakyReLU and the weighted accumulation run on fp32 PAIRS (FFMA2 / FMUL2)
+            uint4 v[4][F / 8];
 #pragma unroll
-                for (int k = 0; k < F; k += 8) {
-                    uint4 v = *reinterpret_cast<const uint4 *>(f + k);
-                    const T *e = reinterpret_cast<const T *>(&v);
-                    if (p.feat_ss) {
+            for (int m = 0; m < 4; ++m) {
+                if (m >= p.M) break;
+                bool fh = false, fw = false;
+                if (p.mirror_mask == 3) { fh = (m & 1) != 0; fw = (m & 2) != 0; }
+                else if (p.mirror_mask == 1) fh = (m == 1);
+                else if (p.mirror_mask == 2) fw = (m == 1);
+                const int sy = fh ? p.Ph - 1 - ly : ly, sx = fw ? p.Pw - 1 - lx : lx;
+                const T *f = feat + (((long long)(t * p.M + m) * p.Ph + sy) * p.Pw + sx) * F;
 #pragma unroll
-                        for (int j = 0; j < 8; j += 2) {
-                            const float4 c = __ldg(ss + (k + j) / 2);
-                            float y0 = fmaf(to_f32<T>(e[j]), c.x, c.y), y1 = fmaf(to_f32<T>(e[j + 1]), c.z, c.w);
-                            y0 = y0 > 0.f ? y0 : y0 * p.slope;
-                            y1 = y1 > 0.f ? y1 : y1 * p.slope;
-                            acc[k + j] = fmaf(gm, to_f32<T>(from_f32<T>(y0)), acc[k + j]);          // rounded to T like norm_act_kernel's output
-                            acc[k + j + 1] = fmaf(gm, to_f32<T>(from_f32<T>(y1)), acc[k + j + 1]);
+                for (int k = 0; k < F / 8; ++k) v[m][k] = ld_stream_16(f + 8 * k);
+            }
+            const uint64_t gm2 = f32x2_pack(gm, gm);
+#pragma unroll
+            for (int m = 0; m < 4; ++m) {
+                if (m >= p.M) break;
+                const float4 *ss = reinterpret_cast<const float4 *>(p.feat_ss) + (long long)(t * p.M + m) * (F / 2);    // warp-uniform broadcast loads
+#pragma unroll
+                for (int k = 0; k < F / 8; ++k) {
+                    const uint32_t *w = reinterpret_cast<const uint32_t *>(&v[m][k]);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const int kp = k * 4 + j;
+                        uint64_t x2;
+                        if constexpr (std::is_same<T, __nv_bfloat16>::value) x2 = f32x2_pack_bits(w[j] << 16, w[j] & 0xffff0000u);
+                        else { const float2 e = unpack2<T>(w[j]); x2 = f32x2_pack(e.x, e.y); }
+                        if (p.feat_ss) {
+                            const float4 c = __ldg(ss + kp);
+                            const uint64_t y2 = f32x2_fma(x2, f32x2_pack(c.x, c.y), f32x2_pack(c.z, c.w));
+                            const uint64_t z2 = f32x2_mul(y2, slope2);
+                            const float y0 = f32x2_lo(y2), y1 = f32x2_hi(y2), z0 = f32x2_lo(z2), z1 = f32x2_hi(z2);
+                            x2 = slope01 ? f32x2_pack(fmaxf(y0, z0), fmaxf(y1, z1)) : f32x2_pack(y0 > 0.f ? y0 : z0, y1 > 0.f ? y1 : z1);
                         }
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) acc[k + j] = fmaf(gm, to_f32<T>(e[j]), acc[k + j]);
+                        acc2[kp] = f32x2_fma(gm2, x2, acc2[kp]);
                     }
                 }
-            } else {
-                const float2 *ss = reinterpret_cast<const float2 *>(p.feat_ss) + (long long)(t * p.M + m) * F;
+            }
+        } else {
+            for (int m = 0; m < p.M; ++m) {
+                bool fh = false, fw = false;
+                if (p.mirror_mask == 3) { fh = (m == 1 || m == 3); fw = (m == 2 || m == 3); }
+                else if (p.mirror_mask == 1) fh = (m == 1);
+                else if (p.mirror_mask == 2) fw = (m == 1);
+                const int sy = fh ? p.Ph - 1 - ly : ly, sx = fw ? p.Pw - 1 - lx : lx;
+                const T *f = feat + (((long long)(t * p.M + m) * p.Ph + sy) * p.Pw + sx) * F;
+                const float *ss = p.feat_ss + (long long)(t * p.M + m) * F * 2;
 #pragma unroll
                 for (int k = 0; k < F; ++k) {
                     float v = to_f32<T>(f[k]);
                     if (p.feat_ss) {
-                        const float2 c = __ldg(ss + k);
-                        v = fmaf(v, c.x, c.y);
+                        const float sc = __ldg(ss + (k >> 1) * 4 + (k & 1)), sh = __ldg(ss + (k >> 1) * 4 + 2 + (k & 1));
+                        v = fmaf(v, sc, sh);
                         v = v > 0.f ? v : v * p.slope;
-                        v = to_f32<T>(from_f32<T>(v));
                     }
                     acc[k] = fmaf(gm, v, acc[k]);
                 }
@@ -392,31 +420,62 @@ __global__ void __launch_bounds__(128) blend_head_kernel(const BlendParams p, co
         }
     }
     const float inv = 1.0f / wsum;
+    if constexpr (sizeof(T) == 2 && (F % 8) == 0) {
+        const uint64_t inv2 = f32x2_pack(inv, inv);
 #pragma unroll
-    for (int k = 0; k < F; ++k) acc[k] *= inv;
+        for (int k = 0; k < F / 2; ++k) acc2[k] = f32x2_mul(acc2[k], inv2);
+    } else {
+#pragma unroll
+        for (int k = 0; k < F; ++k) acc[k] *= inv;
+    }
     const int lane = threadIdx.x & 31;
     for (int c = 0; c < p.heads; ++c) {
         float v = s_head[p.heads * F + c];
+        if constexpr (sizeof(T) == 2 && (F % 8) == 0) {
+            const float4 *hw = reinterpret_cast<const float4 *>(s_head + c * F);       // warp-uniform 16-byte broadcast loads
+            uint64_t d2 = 0ull;
 #pragma unroll
-        for (int k = 0; k < F; ++k) v = fmaf(s_head[c * F + k], acc[k], v);
+            for (int k = 0; k < F / 4; ++k) {
+                const float4 q = hw[k];
+                d2 = f32x2_fma(f32x2_pack(q.x, q.y), acc2[2 * k], d2);
+                d2 = f32x2_fma(f32x2_pack(q.z, q.w), acc2[2 * k + 1], d2);
+            }
+            v += f32x2_lo(d2) + f32x2_hi(d2);
+        } else {
+#pragma unroll
+            for (int k = 0; k < F; ++k) v = fmaf(s_head[c * F + k], acc[k], v);
+        }
         const bool on = active && v > 0.f;
         if (p.logits && active) p.logits[((long long)c * p.h + y) * p.w + x] = v;
         if (p.mask) s_mask[threadIdx.x * p.heads + c] = on ? 1 : 0;
         if (p.present) {
+            // label seen by this warp -> block flag in shared memory (benign race); the global flag is written once per block
+            // below, and only while it still reads 0: per-warp stores to ONE address from all SMs serialise in L2 and used
+            // to cost more than the rest of the kernel
             const unsigned any = __ballot_sync(0xffffffffu, on);
-            if (any && lane == 0) p.present[p.ch_off + c] = 1;
+            if (any && lane == 0) s_any[c] = 1;
         }
     }
+    if (p.present) {
+        __syncthreads();
+        for (int c = threadIdx.x; c < p.heads; c += blockDim.x)
+            if (s_any[c] && __ldcg(p.present + p.ch_off + c) == 0) p.present[p.ch_off + c] = 1;
+    }
     if (p.mask) {
-        // the block's 128 pixels x heads bytes leave through shared memory so that consecutive threads write consecutive bytes
-        // of a pixel's channel window (runs of `heads` bytes at a pitch of ch_total) instead of 32 scattered bytes per store
+        // the block's 128 pixels x heads bytes leave through shared memory: a warp writes one pixel's channel window per
+        // instruction (`heads` consecutive bytes at a pitch of ch_total); the pixel's byte offset comes from its own thread.
+        // Pixels of a block are consecutive, so the first n_here are the active ones; the loop is unrolled so that the
+        // shared-memory loads of 8 pixels are in flight together.
+        long long *s_base = reinterpret_cast<long long *>(s_head) + ((p.heads * F + p.heads) * 4 + 128 * p.heads + 7) / 8;
+        s_base[threadIdx.x] = ((long long)(p.h0 + y) * p.W0 + (p.w0 + x)) * p.ch_total + p.ch_off;
         __syncthreads();
         const int n_here = (int)min((long long)blockDim.x, npix - pix0);
-        for (int i = threadIdx.x; i < n_here * p.heads; i += blockDim.x) {
-            const int pp = i / p.heads, c = i - pp * p.heads;
-            const long long gp = pix0 + pp;
-            const int yy = (int)(gp / p.w), xx = (int)(gp % p.w);
-            p.mask[((long long)(p.h0 + yy) * p.W0 + (p.w0 + xx)) * p.ch_total + p.ch_off + c] = s_mask[i];
+        const int wrp = threadIdx.x >> 5;
+#pragma unroll 8
+        for (int j = 0; j < 32; ++j) {
+            const int pp = wrp * 32 + j;
+            if (pp < n_here)
+                for (int c = lane; c < p.heads; c += 32) p.mask[s_base[pp] + c] = s_mask[pp * p.heads + c];
         }
     }
 }
