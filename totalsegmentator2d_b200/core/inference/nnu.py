@@ -173,7 +173,7 @@ class NNUDeviceModel(NNUModel):
 
     def predict_device(self, img_dev: torch.Tensor, spacing_xy, mask: Optional[torch.Tensor] = None, ch_off: int = 0,
                        present: Optional[torch.Tensor] = None, cache: Optional[dict] = None, cache_key=(),
-                       prepare_only: bool = False) -> torch.Tensor:
+                       prepare_only: bool = False, bbox_future=None) -> torch.Tensor:
         """(C, H, W) float32 CUDA image -> uint8 mask [H][W][ch_total] on the device (this model's channel window).
         Stage order = reference prediction_worker.py:194-221: preprocess -> predict -> export.
         ``prepare_only`` stops after preprocessing + tiling (fills ``cache``): the caller then runs the models on
@@ -185,7 +185,8 @@ class NNUDeviceModel(NNUModel):
         key = self.preprocess_key() + tuple(cache_key)
         entry = cache.get(key) if cache is not None else None
         if entry is None:
-            data, props = B200Preprocessor().run_case_device(img_dev, spacing_xy, p.plans_manager, p.configuration_manager, self.dataset_json)
+            data, props = B200Preprocessor().run_case_device(img_dev, spacing_xy, p.plans_manager, p.configuration_manager, self.dataset_json,
+                                                             bbox_future=bbox_future)
             x, layout = p.make_tiles(data)
             entry = (data.shape, props, x, layout)
             if cache is not None:

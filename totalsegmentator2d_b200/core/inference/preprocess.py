@@ -39,8 +39,9 @@ class B200Preprocessor:
 
     # ---- device path ---------------------------------------------------------------------------
     def run_case_device(self, img: torch.Tensor, spacing_xy: Sequence[float], plans_manager, configuration_manager,
-                        dataset_json=None) -> Tuple[torch.Tensor, dict]:
-        """img: float32 CUDA tensor (C, H, W). returns (data (C, h, w) float32 CUDA, properties)."""
+                        dataset_json=None, bbox_future=None) -> Tuple[torch.Tensor, dict]:
+        """img: float32 CUDA tensor (C, H, W). returns (data (C, h, w) float32 CUDA, properties).
+        ``bbox_future``: (pinned int32[4], event, ...) of a crop box that was already computed for ``img`` on another stream."""
         L.load(check_device=False)
         if img.dtype != torch.float32:
             img = img.to(torch.float32)
@@ -53,7 +54,11 @@ class B200Preprocessor:
             raise RuntimeError("use_mask_for_norm=True is not supported by the B200 preprocessor")
         spacing = sitkio_spacing_2d(spacing_xy)
         props = {"spacing": spacing, "shape_before_cropping": (1, H, W)}
-        bbox = [int(v) for v in ops.bbox_nonzero(img).tolist()]          # one 16-byte D2H per image
+        if bbox_future is not None:
+            bbox_future[1].synchronize()
+            bbox = [int(v) for v in bbox_future[0].tolist()]
+        else:
+            bbox = [int(v) for v in ops.bbox_nonzero(img).tolist()]      # one 16-byte D2H per image (host sync)
         h0, h1, w0, w1 = bbox
         props["bbox_used_for_cropping"] = [[0, 1], [h0, h1], [w0, w1]]
         props["shape_after_cropping_and_before_resampling"] = (1, h1 - h0, w1 - w0)

@@ -120,7 +120,7 @@ class TS2D:
         return [int(v) for v in np.concatenate([[0], np.cumsum(heads)])]
 
     def predict_image_device(self, imgs_dev: Dict[str, torch.Tensor], spacing_xy, mask: Optional[torch.Tensor] = None,
-                             present: Optional[torch.Tensor] = None) -> dict:
+                             present: Optional[torch.Tensor] = None, bbox_futures: Optional[dict] = None) -> dict:
         """imgs_dev: {model id: float32 CUDA (C, H, W)} -> {'mask': uint8 [H][W][sum heads] (model-id order, label order),
         'present': uint8 [sum heads], 'offsets': channel window of each model}.  Everything stays in HBM.
         Models whose preprocessing agrees share the preprocessed image and its tiles (the reference preprocesses
@@ -143,7 +143,8 @@ class TS2D:
             if not side:
                 for k, id in enumerate(ids):
                     key = (imgs_dev[id].data_ptr(),)
-                    self.models[id].predict_device(imgs_dev[id], spacing_xy, mask=mask, ch_off=offs[k], present=present, cache=cache, cache_key=key)
+                    self.models[id].predict_device(imgs_dev[id], spacing_xy, mask=mask, ch_off=offs[k], present=present, cache=cache, cache_key=key,
+                                                   bbox_future=(bbox_futures or {}).get(imgs_dev[id].data_ptr()))
             else:
                 # the group models of one study are independent (reference tool.py:110-112 loops over them): preprocess and
                 # tile once on the caller's stream, then fan the U-Nets out over side streams so that the latency-bound
@@ -153,7 +154,7 @@ class TS2D:
                 for k, id in enumerate(ids):
                     key = (imgs_dev[id].data_ptr(),)
                     self.models[id].predict_device(imgs_dev[id], spacing_xy, mask=mask, ch_off=offs[k], present=present, cache=cache,
-                                                   cache_key=key, prepare_only=True)
+                                                   cache_key=key, prepare_only=True, bbox_future=(bbox_futures or {}).get(imgs_dev[id].data_ptr()))
                 fork = torch.cuda.Event()
                 fork.record(cur)
                 joins = []
@@ -185,11 +186,12 @@ class TS2D:
             pool = self._side_streams = [torch.cuda.Stream() for _ in range(want)]
         return pool
 
-    def predict_volume_device(self, vol_dev: torch.Tensor, spacing_xyz, direction=None, mask: Optional[torch.Tensor] = None,
-                              present: Optional[torch.Tensor] = None) -> dict:
-        """vol_dev: CUDA tensor [z][y][x] (sitk.GetArrayFromImage order) -> projections + merged mask, all in HBM.
-        reorient_image('RAI') (reference tool.py:154) is folded into the projection kernel's addressing; every channel
-        any model asks for comes out of one pass over the volume (reference: one ITK filter per channel, tool.py:156-159)."""
+    def project_volume_device(self, vol_dev: torch.Tensor, spacing_xyz, direction=None, bbox_async: bool = False) -> dict:
+        """vol_dev: CUDA tensor [z][y][x] (sitk.GetArrayFromImage order) -> every projection channel any model asks for, from
+        ONE pass over the volume (reference: one ITK filter per channel and model, tool.py:156-159); reorient_image('RAI')
+        (tool.py:154) is folded into the kernel's addressing.  With ``bbox_async`` the crop_to_nonzero bounding box of each
+        model input is computed right away and copied to pinned host memory without waiting (the caller synchronises on the
+        event when it needs the numbers), so that no host sync sits between the upload and the U-Nets."""
         chan_defs = self._channel_defs()
         names: List[str] = []
         for id in self.models:
@@ -208,8 +210,30 @@ class TS2D:
                 stacked[idx] = out if idx == tuple(range(len(names))) else torch.stack([out[i] for i in idx], dim=0)
             imgs[id] = stacked[idx]
         sp = [float(spacing_xyz[perm[k]]) for k in range(3)]
-        res = self.predict_image_device(imgs, (sp[0], sp[2]), mask=mask, present=present)
-        res["projections"], res["channel_names"] = out, names
+        st = {"projections": out, "channel_names": names, "imgs": imgs, "spacing_xy": (sp[0], sp[2]), "bbox_futures": None}
+        if bbox_async:
+            st["bbox_futures"] = self._bbox_futures(stacked.values())
+        return st
+
+    @staticmethod
+    def _bbox_futures(images) -> dict:
+        futures = dict()
+        for img in images:
+            bb = ops.bbox_nonzero(img.contiguous())
+            host = torch.empty(4, dtype=torch.int32, pin_memory=True)
+            host.copy_(bb, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record()
+            futures[img.data_ptr()] = (host, ev, bb)
+        return futures
+
+    def predict_volume_device(self, vol_dev: torch.Tensor, spacing_xyz, direction=None, mask: Optional[torch.Tensor] = None,
+                              present: Optional[torch.Tensor] = None, projected: Optional[dict] = None) -> dict:
+        """vol_dev: CUDA tensor [z][y][x] -> projections + merged mask, all in HBM (``projected``: the result of an earlier
+        ``project_volume_device`` call for this volume, e.g. issued on the upload stream)."""
+        st = projected if projected is not None else self.project_volume_device(vol_dev, spacing_xyz, direction)
+        res = self.predict_image_device(st["imgs"], st["spacing_xy"], mask=mask, present=present, bbox_futures=st["bbox_futures"])
+        res["projections"], res["channel_names"] = st["projections"], st["channel_names"]
         return res
 
     # ------------------------------------------------------------------------------------------------
@@ -222,13 +246,20 @@ class TS2D:
         """
         return self._finish(self._submit(input, collapse, merge))
 
-    def predict_batch(self, inputs, collapse: bool = False, merge: bool = True, depth: int = 2):
+    def predict_batch(self, inputs, collapse: bool = False, merge: bool = True, depth: int = 2, lookahead: int = 1):
         """Generator over ``predict`` results for a sequence of inputs (the reference CLI loops over its inputs one by one,
-        ts2d/main.py:80-83).  Software pipeline over three CUDA streams: while study i computes, study i+1 is uploaded and
-        the mask of study i-1 is downloaded and wrapped on the host.  Results come out in input order."""
-        pending = []
+        ts2d/main.py:80-83).  Software pipeline over CUDA streams: input i+1.. is uploaded and projected (and its crop box is
+        on its way to the host) while study i computes and the mask of study i-1 is downloaded and wrapped on the host; the
+        host never waits for the GPU between the upload and the U-Nets.  Results come out in input order."""
+        staged, pending = [], []
         for inp in inputs:
-            pending.append(self._submit(inp, collapse, merge))
+            staged.append(self._stage_upload(inp, collapse, merge))
+            if len(staged) > max(0, lookahead):
+                pending.append(self._stage_compute(staged.pop(0)))
+            if len(pending) >= max(1, depth):
+                yield self._finish(pending.pop(0))
+        while staged:
+            pending.append(self._stage_compute(staged.pop(0)))
             if len(pending) >= max(1, depth):
                 yield self._finish(pending.pop(0))
         while pending:
@@ -245,7 +276,11 @@ class TS2D:
         return torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
 
     def _submit(self, input, collapse: bool, merge: bool) -> dict:
-        """enqueues upload, device pipeline and download of one input; nothing here waits for the GPU"""
+        """enqueues upload, device pipeline and download of one input"""
+        return self._stage_compute(self._stage_upload(input, collapse, merge))
+
+    def _stage_upload(self, input, collapse: bool, merge: bool) -> dict:
+        """upload stream: H2D copy of the input, projection (3-D inputs) and the crop box of every model input; nothing waits"""
         if isinstance(input, str):
             input = read_image(input)
         try:
@@ -256,17 +291,14 @@ class TS2D:
         is3d = get_actual_dimension(input) > 2
         chan_defs = self._channel_defs()
         h2d, d2h = self._streams()
-        cur = torch.cuda.current_stream()
         job = {"input": input, "collapse": collapse, "merge": merge, "is3d": is3d, "chan_defs": chan_defs, "keep": []}
         if is3d:
             with torch.cuda.stream(h2d):
                 vol = _to_device(input.array)
+                job["projected"] = self.project_volume_device(vol, input.GetSpacing(), input.direction_matrix(), bbox_async=True)
                 ev = torch.cuda.Event()
                 ev.record(h2d)
-            cur.wait_event(ev)
-            vol.record_stream(cur)
-            dev = self.predict_volume_device(vol, input.GetSpacing(), input.direction_matrix())
-            del vol
+            job["vol"] = vol
         else:
             base2d = input if input.GetDimension() < 3 else reduce_dimensions(input)
             input_nch = input.GetNumberOfComponentsPerPixel()
@@ -277,12 +309,35 @@ class TS2D:
             chw = np.moveaxis(arr, -1, 0) if base2d.is_vector else arr[None]
             with torch.cuda.stream(h2d):
                 img_dev_2d = torch.from_numpy(np.ascontiguousarray(chw)).cuda(non_blocking=True)
+                job["bbox_futures"] = self._bbox_futures([img_dev_2d])
                 ev = torch.cuda.Event()
                 ev.record(h2d)
-            cur.wait_event(ev)
-            img_dev_2d.record_stream(cur)
-            dev = self.predict_image_device({id: img_dev_2d for id in ids}, base2d.GetSpacing())
+            job["img2d"] = img_dev_2d
             job["base2d"] = base2d
+        job["uploaded"] = ev
+        return job
+
+    def _stage_compute(self, job: dict) -> dict:
+        """compute stream: the five U-Nets, blend / threshold and the merged channel order; download stream: results to pinned memory"""
+        input, merge, is3d = job["input"], job["merge"], job["is3d"]
+        ids = list(self.models.keys())
+        h2d, d2h = self._streams()
+        cur = torch.cuda.current_stream()
+        cur.wait_event(job.pop("uploaded"))
+        if is3d:
+            vol, st = job.pop("vol"), job.pop("projected")
+            vol.record_stream(cur)
+            for t in [st["projections"]] + list(st["imgs"].values()) + [f[2] for f in (st["bbox_futures"] or {}).values()]:
+                t.record_stream(cur)
+            dev = self.predict_volume_device(vol, input.GetSpacing(), input.direction_matrix(), projected=st)
+            del vol
+        else:
+            img_dev_2d = job.pop("img2d")
+            img_dev_2d.record_stream(cur)
+            futs = job.pop("bbox_futures")
+            for f in futs.values():
+                f[2].record_stream(cur)
+            dev = self.predict_image_device({id: img_dev_2d for id in ids}, job["base2d"].GetSpacing(), bbox_futures=futs)
         mask, present, offs = dev["mask"], dev["present"], dev["offsets"]
         job.update(mask=mask, offs=offs, channel_names=dev.get("channel_names"))
         merged_dev = perm_dev = None
