@@ -74,6 +74,31 @@ def test_tensor_core_equals_direct_same_precision():
     assert float((a - b).abs().max()) <= 2e-2, float((a - b).abs().max())
 
 
+@pytest.mark.parametrize("precision,tol", [("bf16", 0.03), ("fp16", 0.004)])
+@pytest.mark.parametrize("patch", [(40, 72), (16, 8), (48, 36)])
+def test_first_conv_tensor_core(precision, tol, patch, monkeypatch):
+    """conv_first_tc_kernel (im2col rows built by the workers, bias in two extra K columns): first layer against the fp32
+    oracle on patches whose 8 x 16 pixel tiles overhang the image, whose border tiles are the majority, and with 64 output
+    channels (two channel blocks); and against the CUDA-core first-layer kernel (TS2D_FIRST_TC=0)."""
+    dt = torch.bfloat16 if precision == "bf16" else torch.float16
+    outs = []
+    for first_tc in ("1", "0"):
+        monkeypatch.setenv("TS2D_FIRST_TC", first_tc)
+        p, sd, spec = _make([64, 64], patch, heads=3, precision=precision, seed=21, strides=[[1, 1], [2, 2]])
+        x, xd = _tiles(3, 2, patch, 5, dt)
+        x = xd.float().cpu().permute(0, 3, 1, 2).contiguous()
+        coll = {}
+        with torch.no_grad():
+            nnunet_net.unet_forward(x, sd, spec, collect=coll)
+        ref = coll["enc0.0"]
+        got = p.forward_debug(xd, "enc0.0", tuple(ref.shape[1:])).cpu()
+        outs.append(got)
+        assert float((got - ref).abs().max()) <= tol, (first_tc, float((got - ref).abs().max()))
+        p.close()
+    # the two kernels round the same fp32 sums independently: at most one storage ulp apart (2^-5 for |x| in [4, 8) in bf16)
+    assert float((outs[0] - outs[1]).abs().max()) <= 2 * tol
+
+
 def test_tensor_core_ragged_tiles_and_small_levels():
     """W=160/80/40/20 (tiles overhang the image), deepest level 5x3.. covers masked rows and multi-image tiles"""
     p, sd, spec = _make([32, 32, 64, 64, 64], (48, 160), heads=4, precision="fp16", seed=9)

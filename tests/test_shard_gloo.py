@@ -60,3 +60,59 @@ def test_single_process_fallbacks():
     assert shard.gather_in_order([1, 2], 2) == [1, 2]
     with pytest.raises(ValueError):
         shard.shard_indices(3, 2, 2)
+
+
+def _latency_worker(rank, world, port, home, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        widths = [18, 23, 24, 26, 26]                      # ts2d-v2 heads per group model
+        H, W = 20, 12
+        img = torch.arange(2 * H * W, dtype=torch.float32).reshape(2, H, W) if rank == home else None
+        img, meta = shard.broadcast_image(img, home, meta=(1.5, 0.75))
+        mine = shard.owned_models(len(widths), rank, world, home)
+        # "model" k marks its window with k + 1 wherever the broadcast image is odd
+        odd = (img[0].to(torch.int64) % 2 == 1)
+        local = {k: (odd[..., None] * (k + 1)).expand(H, W, widths[k]).to(torch.uint8).contiguous() for k in mine}
+        present = {k: torch.full((widths[k],), k + 1, dtype=torch.uint8) for k in mine}
+        mask = shard.gather_windows(local, len(widths), widths, (H, W), home, dtype=torch.uint8)
+        pres = shard.gather_windows(present, len(widths), widths, (), home, dtype=torch.uint8)
+        q.put((rank, mine, meta, None if mask is None else mask.clone(), None if pres is None else pres.clone(), tuple(img.shape)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,home", [(2, 0), (2, 1), (3, 1)])
+def test_latency_mode_broadcast_and_gather(world, home):
+    """one study over `world` ranks: image broadcast from the home rank, per-model windows gathered back in model order"""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_latency_worker, args=(r, world, port, home, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    out = {r[0]: r for r in (q.get(timeout=120) for _ in range(world))}
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    widths = [18, 23, 24, 26, 26]
+    assert sorted(k for r in out.values() for k in r[1]) == [0, 1, 2, 3, 4], "every group model runs exactly once"
+    assert 0 in out[home][1], "the home rank runs the first model itself"
+    for rank, (_, mine, meta, mask, pres, shape) in out.items():
+        assert shape == (2, 20, 12) and meta[:2] == [1.5, 0.75]
+        assert (mask is None) == (rank != home)
+    mask, pres = out[home][3], out[home][4]
+    odd = (torch.arange(20 * 12).reshape(20, 12) % 2 == 1)
+    off = 0
+    for k, w in enumerate(widths):
+        assert torch.equal(mask[..., off:off + w], (odd[..., None] * (k + 1)).expand(20, 12, w).to(torch.uint8))
+        assert torch.equal(pres[off:off + w], torch.full((w,), k + 1, dtype=torch.uint8))
+        off += w
+
+
+def test_model_owner_round_robin():
+    assert [shard.model_owner(k, 8, 3) for k in range(5)] == [3, 4, 5, 6, 7]
+    assert shard.owned_models(5, 0, 2) == [0, 2, 4] and shard.owned_models(5, 1, 2) == [1, 3]
+    assert shard.owned_models(5, 0, 1) == [0, 1, 2, 3, 4]
+    with pytest.raises(ValueError):
+        shard.model_owner(0, 2, 2)

@@ -305,7 +305,7 @@ static int launch_first_tc(const FirstTcParams &p, cudaStream_t st) {
 }
 // tensor-core first conv (conv_first_tc_kernel): two 16-bit input channels, output channels in blocks of 32
 static bool first_tc_eligible(const ts2d_unet_plan &pl, const ConvLayer &c) {
-    static const int enable = getenv("TS2D_FIRST_TC") ? atoi(getenv("TS2D_FIRST_TC")) : 1;
+    const int enable = getenv("TS2D_FIRST_TC") ? atoi(getenv("TS2D_FIRST_TC")) : 1;
     return enable && pl.use_tensor_cores && pl.precision != TS2D_PREC_F32 && c.kh == 3 && c.kw == 3 && c.sh == 1 && c.sw == 1 && c.cin == 2 &&
            c.cout % 32 == 0 && c.in_ps == c.cin;
 }

@@ -76,3 +76,89 @@ def gather_in_order(local_records: Sequence[Any], n_items: int) -> List[Any]:
         for k, i in enumerate(shard_indices(n_items, r, world)):
             out[i] = parts[r][k]
     return out
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Latency mode: ONE study spread over the ranks.  The group models of a study are independent (reference
+# ts2d/tool.py:110-112) and share only the projected image, so the home rank projects, broadcasts the 4 MB image, every
+# rank runs the group models it owns, and the per-model label masks are gathered on the home rank (the only exchange
+# step of the path; NCCL over NVLink on the GPU box, gloo in the CPU tests).
+# ------------------------------------------------------------------------------------------------------------------
+def model_owner(k: int, world: int, home: int = 0) -> int:
+    """rank that runs group model k of a study whose volume lives on rank `home` (round robin starting at home)"""
+    if world < 1 or not (0 <= home < world) or k < 0:
+        raise ValueError(f"invalid model {k} / home {home} / world {world}")
+    return (home + k) % world
+
+
+def owned_models(n_models: int, rank: int, world: int, home: int = 0) -> List[int]:
+    return [k for k in range(n_models) if model_owner(k, world, home) == rank]
+
+
+def broadcast_image(img, src: int, meta: Sequence[float] = (), header_len: int = 8):
+    """rank `src` passes `img` (C, H, W) float32 and up to 5 numbers `meta` (e.g. the pixel spacing); every rank returns
+    (img, meta).  Two broadcasts: a fixed-size float64 header (shape + meta), then the pixels."""
+    import torch
+    d = _dist()
+    if d is None:
+        return img, [float(v) for v in meta]
+    dev = _device()
+    rank = d.get_rank()
+    n_meta = header_len - 3
+    hdr = torch.zeros(header_len, dtype=torch.float64)
+    if rank == src:
+        if len(meta) > n_meta:
+            raise ValueError("too many meta values")
+        hdr[:3] = torch.tensor([float(v) for v in img.shape], dtype=torch.float64)
+        hdr[3:3 + len(meta)] = torch.tensor([float(v) for v in meta], dtype=torch.float64)
+    hdr = hdr.to(dev)
+    d.broadcast(hdr, src=src)
+    vals = hdr.tolist()
+    C, H, W = (int(v) for v in vals[:3])
+    if rank != src:
+        img = torch.empty((C, H, W), dtype=torch.float32, device=dev)
+    else:
+        img = img.contiguous()
+    d.broadcast(img, src=src)
+    return img, vals[3:]
+
+
+def gather_windows(local: dict, n_models: int, widths: Sequence[int], lead_shape: Sequence[int], home: int, out=None, dtype=None):
+    """local: {model index k: tensor [*lead_shape, widths[k]]} for the models this rank owns.  On the home rank returns
+    `out` [*lead_shape, sum(widths)] with every model's window in place (model-id order); other ranks return None.
+    One batch of point-to-point transfers: sizes are known on every rank, nothing is padded."""
+    import torch
+    d = _dist()
+    offs = [0]
+    for w in widths:
+        offs.append(offs[-1] + int(w))
+    if d is None:
+        world, rank = 1, 0
+    else:
+        world, rank = d.get_world_size(), d.get_rank()
+    mine = owned_models(n_models, rank, world, home)
+    if sorted(local.keys()) != mine:
+        raise ValueError(f"rank {rank} holds windows {sorted(local.keys())}, expected {mine}")
+    if rank == home:
+        any_t = next(iter(local.values())) if local else None
+        if out is None:
+            out = torch.zeros((*lead_shape, offs[-1]), dtype=dtype or any_t.dtype, device=any_t.device if any_t is not None else _device())
+        ops, bufs = [], {}
+        for k in range(n_models):
+            o = model_owner(k, world, home)
+            if o == home:
+                out[..., offs[k]:offs[k + 1]].copy_(local[k])
+            else:
+                bufs[k] = torch.empty((*lead_shape, int(widths[k])), dtype=out.dtype, device=out.device)
+                ops.append(d.P2POp(d.irecv, bufs[k], o))
+        if ops:
+            for r in d.batch_isend_irecv(ops):
+                r.wait()
+        for k, b in bufs.items():
+            out[..., offs[k]:offs[k + 1]].copy_(b)
+        return out
+    ops = [d.P2POp(d.isend, local[k].contiguous(), home) for k in mine]
+    if ops:
+        for r in d.batch_isend_irecv(ops):
+            r.wait()
+    return None

@@ -192,28 +192,38 @@ class TS2D:
         (tool.py:154) is folded into the kernel's addressing.  With ``bbox_async`` the crop_to_nonzero bounding box of each
         model input is computed right away and copied to pinned host memory without waiting (the caller synchronises on the
         event when it needs the numbers), so that no host sync sits between the upload and the U-Nets."""
+        names = self._projection_names()
+        d = np.eye(3) if direction is None else np.asarray(direction, dtype=np.float64).reshape(3, 3)
+        perm, flip = orientation_remap(d, "RAI")
+        ax = axis_name_to_index("coronal")
+        out = ops.project(vol_dev, names, reduce_dim=2 - perm[ax], h_dim=2 - perm[2], flip_h=flip[2], flip_w=flip[0])
+        imgs = self._model_inputs(out, names)
+        sp = [float(spacing_xyz[perm[k]]) for k in range(3)]
+        st = {"projections": out, "channel_names": names, "imgs": imgs, "spacing_xy": (sp[0], sp[2]), "bbox_futures": None}
+        if bbox_async:
+            st["bbox_futures"] = self._bbox_futures({t.data_ptr(): t for t in imgs.values()}.values())
+        return st
+
+    def _projection_names(self) -> List[str]:
+        """every projection channel any model asks for, in first-use order (reference tool.py:145-159)"""
         chan_defs = self._channel_defs()
         names: List[str] = []
         for id in self.models:
             for _, n in chan_defs[id]:
                 if n not in names:
                     names.append(n)
-        d = np.eye(3) if direction is None else np.asarray(direction, dtype=np.float64).reshape(3, 3)
-        perm, flip = orientation_remap(d, "RAI")
-        ax = axis_name_to_index("coronal")
-        out = ops.project(vol_dev, names, reduce_dim=2 - perm[ax], h_dim=2 - perm[2], flip_h=flip[2], flip_w=flip[0])
-        imgs = dict()
-        stacked = dict()
+        return names
+
+    def _model_inputs(self, out: torch.Tensor, names: List[str]) -> Dict[str, torch.Tensor]:
+        """per model the channels it asks for, ascending channel index (reference tool.py:148,160); models that agree share the tensor"""
+        chan_defs = self._channel_defs()
+        imgs, stacked = dict(), dict()
         for id in self.models:
             idx = tuple(names.index(n) for _, n in chan_defs[id])
             if idx not in stacked:
                 stacked[idx] = out if idx == tuple(range(len(names))) else torch.stack([out[i] for i in idx], dim=0)
             imgs[id] = stacked[idx]
-        sp = [float(spacing_xyz[perm[k]]) for k in range(3)]
-        st = {"projections": out, "channel_names": names, "imgs": imgs, "spacing_xy": (sp[0], sp[2]), "bbox_futures": None}
-        if bbox_async:
-            st["bbox_futures"] = self._bbox_futures(stacked.values())
-        return st
+        return imgs
 
     @staticmethod
     def _bbox_futures(images) -> dict:
@@ -235,6 +245,51 @@ class TS2D:
         res = self.predict_image_device(st["imgs"], st["spacing_xy"], mask=mask, present=present, bbox_futures=st["bbox_futures"])
         res["projections"], res["channel_names"] = st["projections"], st["channel_names"]
         return res
+
+    def predict_volume_sharded(self, vol_dev: Optional[torch.Tensor], spacing_xyz=None, direction=None, home: int = 0) -> Optional[dict]:
+        """Latency mode (collective: every rank of the process group calls it): ONE study spread over the GPUs.
+        The home rank holds the volume and projects it; the 4 MB projected image is broadcast; rank r runs the group models
+        ``shard.owned_models`` assigns to it (they are independent, reference tool.py:110-112); the per-model label masks and
+        present flags are gathered on the home rank (the path's only exchange step), which merges them in the reference's
+        channel order.  Returns the same dict as ``predict_volume_device`` plus 'merged' / 'perm' on the home rank, None elsewhere.
+        With one process it degenerates to ``predict_volume_device``."""
+        from . import shard
+        rank, world, _ = shard.rank_world()
+        import torch.distributed as dist
+        if world == 1 or not dist.is_initialized():
+            res = self.predict_volume_device(vol_dev, spacing_xyz, direction)
+            res["merged"], res["perm"] = ops.merge_present_order(res["mask"], res["present"], res["offsets"])
+            return res
+        ids = list(self.models.keys())
+        offs = self.head_offsets()
+        widths = [offs[k + 1] - offs[k] for k in range(len(ids))]
+        st = None
+        if rank == home:
+            st = self.project_volume_device(vol_dev, spacing_xyz, direction)
+            out, meta = shard.broadcast_image(st["projections"], home, meta=st["spacing_xy"])
+        else:
+            out, meta = shard.broadcast_image(None, home)
+        names = st["channel_names"] if st is not None else self._projection_names()
+        imgs = self._model_inputs(out, names)
+        H, W = int(out.shape[1]), int(out.shape[2])
+        local_masks, local_present = dict(), dict()
+        cache = dict()
+        for k in shard.owned_models(len(ids), rank, world, home):
+            id = ids[k]
+            m = torch.zeros((H, W, widths[k]), dtype=torch.uint8, device=out.device)
+            pr = torch.zeros(widths[k], dtype=torch.uint8, device=out.device)
+            try:
+                self.models[id].predict_device(imgs[id], (meta[0], meta[1]), mask=m, ch_off=0, present=pr, cache=cache,
+                                               cache_key=(imgs[id].data_ptr(),))
+            except L.TS2DError as ex:
+                raise RuntimeError(f"Prediction failed for: {id} ({ex})") from ex
+            local_masks[k], local_present[k] = m, pr
+        mask = shard.gather_windows(local_masks, len(ids), widths, (H, W), home, dtype=torch.uint8)
+        present = shard.gather_windows(local_present, len(ids), widths, (), home, dtype=torch.uint8)
+        if rank != home:
+            return None
+        merged, perm = ops.merge_present_order(mask, present, offs)
+        return {"mask": mask, "present": present, "offsets": offs, "projections": out, "channel_names": names, "merged": merged, "perm": perm}
 
     # ------------------------------------------------------------------------------------------------
     def predict(self, input, collapse: bool = False, merge: bool = True):
