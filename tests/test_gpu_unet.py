@@ -162,3 +162,30 @@ def test_deferred_norm_is_bit_identical(precision, monkeypatch):
     # path rounds them to the storage type first): one storage rounding of the 32 features apart
     tol = 5e-2 if precision == "bf16" else 1e-2
     assert float((bl_a - bl_b).abs().max()) <= tol
+
+
+@pytest.mark.parametrize("precision,tol", [("bf16", 0.25), ("fp16", 0.04)])      # five levels deep: a little above the 4-level test
+def test_partial_mode_tiny_levels(precision, tol, monkeypatch):
+    """4x4 / 8x8 levels (several images per 128-pixel tile): conv_tc_kernel stores fp32 accumulators ("partial" mode, optionally with K
+    split over 3 or 9 tap groups on separate CTAs) and splitk_finish_kernel = slice sum + bias + InstanceNorm statistics + normalise +
+    LeakyReLU, against the epilogue-atomics + norm_act_kernel path (TS2D_KSPLIT=0) and the fp32 oracle; stride-2 and stride-1 convs."""
+    dt = torch.bfloat16 if precision == "bf16" else torch.float16
+    outs = {}
+    for mode in ("0", "1", "3", "9"):
+        monkeypatch.setenv("TS2D_KSPLIT", mode)
+        p, sd, spec = _make([32, 64, 128, 256, 256], (64, 64), heads=7, precision=precision, seed=5)
+        x, xd = _tiles(3, 2, (64, 64), 2, dt)
+        x = xd.float().cpu().permute(0, 3, 1, 2).contiguous()
+        errs = _layer_errors(p, sd, spec, x, xd)
+        assert max(errs.values()) <= tol, (mode, errs)
+        outs[mode] = (p.forward_debug(xd, "enc4.1", (256, 4, 4)).cpu(), p.predict_tile_logits(xd).cpu())
+        p.close()
+    for mode in ("1", "3", "9"):
+        # same products, different fp32 summation order (and statistics from fp32 sums instead of per-value double atomics)
+        assert float((outs[mode][0] - outs["0"][0]).abs().max()) <= (6e-2 if precision == "bf16" else 8e-3)
+        assert float((outs[mode][1] - outs["0"][1]).abs().max()) <= tol
+    # deterministic: slices are added in a fixed order
+    monkeypatch.setenv("TS2D_KSPLIT", "9")
+    p, sd, spec = _make([32, 64, 128, 256, 256], (64, 64), heads=7, precision=precision, seed=5)
+    again = p.predict_tile_logits(xd).cpu()
+    assert torch.equal(again, outs["9"][1])

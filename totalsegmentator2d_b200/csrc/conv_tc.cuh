@@ -46,6 +46,12 @@ struct ConvTcParams {
     void *out;
     const float *bias;           // [Cout] or null
     double *stats;               // [N][Cout][2] or null
+    // split-K (tiny levels: a handful of M tiles, K = 9*512 .. 9*1024): tile index = (output tile, K slice), slice ks covers
+    // k-chunks [ks*k_chunks/ksplit, (ks+1)*k_chunks/ksplit); the epilogue stores the fp32 accumulators to
+    // partial[ks][(n*Hout + y)*Wout + x][Cout] (no bias / rounding / statistics: splitk_finish_kernel does those in a fixed order)
+    int ksplit;                  // 0 / 1: off
+    float *partial;
+    long long *dbg;              // TS2D_TC_DBG: per-CTA clock stamps (8 per CTA), see run_conv
 };
 constexpr int kTcThreads = 384;
 
@@ -288,6 +294,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+    long long *dbg = p.dbg ? p.dbg + 8 * blockIdx.x : nullptr;
+    const long long t_start = dbg ? clock64() : 0;
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
@@ -304,10 +312,13 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
+    if (dbg && threadIdx.x == 0) dbg[0] = clock64() - t_start;          // prologue (barriers, TMEM allocation)
 
     const int m_tiles = p.tiles_n * p.tiles_h * p.tiles_w;
-    const int total_tiles = m_tiles * p.n_tiles_n;
+    const int ksplit = p.ksplit > 1 ? p.ksplit : 1;
+    const int total_tiles = m_tiles * p.n_tiles_n * ksplit;
     const int k_chunks = p.taps * p.cin_chunks;
+    const int k_per = k_chunks / ksplit;          // k-chunks per tile (the host guarantees divisibility)
     // tile t -> channel block nt = t / m_tiles (slowest), m tile = t % m_tiles = (image group, y tile, x tile) with x fastest
     const int t_begin = (int)((long long)total_tiles * blockIdx.x / gridDim.x);
     const int t_end = (int)((long long)total_tiles * (blockIdx.x + 1) / gridDim.x);
@@ -318,10 +329,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             int stage = 0;
             uint32_t phase = 0;
             for (int tile = t_begin; tile < t_end; ++tile) {
-                const int nt = tile / m_tiles, mt = tile - nt * m_tiles;
+                const int ot = tile / ksplit, ks = tile - ot * ksplit;      // (output tile, K slice), slice fastest
+                const int nt = ot / m_tiles, mt = ot - nt * m_tiles;
                 const int xt = mt % p.tiles_w, yt = (mt / p.tiles_w) % p.tiles_h, nn = mt / (p.tiles_w * p.tiles_h);
                 const int x0 = xt * p.tw, y0 = yt * p.th, n0 = nn * p.tn;
-                for (int kc = 0; kc < k_chunks; ++kc) {
+                for (int kc = ks * k_per; kc < (ks + 1) * k_per; ++kc) {
                     const int tap = kc / p.cin_chunks, cc = kc % p.cin_chunks;
                     const int r = tap / p.kw, s = tap % p.kw;
                     mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -339,8 +351,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     }
                     tma_load_3d(sb, &tmB, &full_bar[stage], cc * KC, nt * BN, tap);
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
+                    if (dbg && tile == t_begin && kc == ks * k_per) dbg[1] = clock64() - t_start;     // first loads issued
                 }
             }
+            if (dbg) dbg[2] = clock64() - t_start;                                                    // all loads issued
         }
     } else if (warp == 1) {
         // ===================== MMA issuer (whole warp convergent, one elected lane issues) =====================
@@ -357,9 +371,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);
             tcgen05_fence_after();
             const uint32_t d_tmem = tmem_base + (uint32_t)(buf * BN);
-            for (int kc = 0; kc < k_chunks; ++kc) {
+            for (int kc = 0; kc < k_per; ++kc) {
                 mbar_wait(&full_bar[stage], phase);
                 tcgen05_fence_after();
+                if (dbg && lane == 0 && it == 0 && kc == 0) dbg[3] = clock64() - t_start;              // first operands landed
                 const uint32_t a_lo = s0_lo + (uint32_t)(stage * (kStageBytes >> 4));
                 const uint32_t b_lo = a_lo + (uint32_t)(kABytes >> 4);
 #pragma unroll
@@ -370,6 +385,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
             tcgen05_commit_pred(leader, &tmem_full[buf]);             // accumulator complete
         }
+        if (dbg && lane == 0) dbg[4] = clock64() - t_start;                                           // all MMAs issued
     } else if (warp >= 4) {
         // ===================== epilogue (warps 4..11, two warpgroups) =====================
         const int grp = (warp - 4) >> 2;
@@ -406,6 +422,41 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const int mt = tile - nt * m_tiles;
             xt = mt % p.tiles_w; yt = (mt / p.tiles_w) % p.tiles_h; nn = mt / (p.tiles_w * p.tiles_h);
         }
+        if (p.partial) {
+            // ---- split-K: fp32 accumulators of K slice ks -> partial[ks][pixel][Cout]; few tiles per CTA, so plain divisions ----
+            const long long mtot = (long long)p.N * p.Hout * p.Wout;
+            for (int e = kAlt ? grp : 0, t = t_begin + e; t < t_end; t += estep, e += estep) {
+                const int ot = t / ksplit, ks = t - ot * ksplit;
+                const int snt = ot / m_tiles, mt = ot - snt * m_tiles;
+                const int sxt = mt % p.tiles_w, syt = (mt / p.tiles_w) % p.tiles_h, snn = mt / (p.tiles_w * p.tiles_h);
+                const int buf = e & 1;
+                const uint32_t par = (uint32_t)(e >> 1) & 1u;
+                const int x = sxt * p.tw + ix, y = syt * p.th + iy, n = snn * p.tn + in_;
+                const bool valid = (x < p.Wout) && (y < p.Hout) && (n < p.N);
+                mbar_wait(&tmem_full[buf], par);
+                tcgen05_fence_after();
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BN);
+                float *prow = p.partial + ((long long)ks * mtot + ((long long)n * p.Hout + y) * p.Wout + x) * p.Cout + snt * BN;
+#pragma unroll
+                for (int c = 0; c < kMyChunks; ++c) {
+                    const int chunk = chunk0 + c;
+                    uint32_t r[32];
+                    tmem_ld_32x32b_x32(taddr + chunk * 32, r);
+                    tmem_ld_wait();
+                    if (c == kMyChunks - 1) {
+                        tcgen05_fence_before();
+                        mbar_arrive(&tmem_empty[buf]);
+                    }
+                    if (valid) {
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(prow + chunk * 32 + 8 * k), "r"(r[8 * k]),
+                                         "r"(r[8 * k + 1]), "r"(r[8 * k + 2]), "r"(r[8 * k + 3]), "r"(r[8 * k + 4]), "r"(r[8 * k + 5]), "r"(r[8 * k + 6]),
+                                         "r"(r[8 * k + 7]) : "memory");
+                    }
+                }
+            }
+        } else
         for (int e = kAlt ? grp : 0; tile < t_end; tile += estep, e += estep) {
             const int buf = e & 1;
             const uint32_t par = (uint32_t)(e >> 1) & 1u;
@@ -478,9 +529,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
         }
         if (fast_stats && cur_n >= 0) flush_stats(cur_n, cur_nt);
+        if (dbg && warp == 4 && lane == 0) dbg[5] = clock64() - t_start;                              // epilogue done
     }
     tcgen05_fence_before();
     __syncthreads();
+    if (dbg && threadIdx.x == 0) dbg[6] = clock64() - t_start;
     if (warp == 1) {
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kTmemCols) : "memory");
     }

@@ -105,6 +105,8 @@ struct ts2d_unet {
     size_t arena_bytes = 0;
     std::vector<void *> cat;
     void *bott = nullptr, *raw = nullptr, *rawB = nullptr, *tmpA = nullptr, *tmpB = nullptr;
+    float *partial = nullptr;     // split-K partial sums of the tiny levels [ksplit][N*HW][Cout] fp32
+    size_t partial_bytes = 0;
     float *feat_ss = nullptr;     // [N][C0][2] scale / shift of the last decoder conv when its norm is deferred to the blend kernel
     double *stats_arena = nullptr;
     size_t stats_bytes = 0;
@@ -139,7 +141,11 @@ static void choose_tile(int Hout, int Wout, int N, int &tw, int &th, int &tn) {
 // output-channel block of conv_tc_kernel from a cycle model of one CTA (measured on B200, tools/probe/mma_rate.cu:
 // an M=128, K=16 tcgen05.mma costs ~45 / 51 / 67 / 131 cycles at N = 32 / 64 / 128 / 256; an epilogue warp needs
 // ~400 cycles per 32-column chunk): time = waves x max(MMA time, epilogue time) per tile.
+static int env_int(const char *name, int dflt) { const char *v = getenv(name); return v ? atoi(v) : dflt; }
+// + kTileOvh cycles per tile (TMA latency of the first chunk, tmem_full / tmem_empty round trips): decides the 1-chunk tiles of the
+// full-resolution transposed conv (BN = 32: 0.125 ms, BN = 128: one pass over A).
 static int choose_bn(int n_total, long long m_tiles, int k_steps) {
+    static const int ovh = env_int("TS2D_TILE_OVH", 600);
     int best_bn = 32;
     double best = 1e30;
     for (int bn : {256, 128, 64, 32}) {
@@ -147,21 +153,31 @@ static int choose_bn(int n_total, long long m_tiles, int k_steps) {
         const double mma = bn == 256 ? 131 : bn == 128 ? 67 : bn == 64 ? 51 : 45;
         const double epi = bn == 32 ? 200 : 400.0 * (bn / 64);
         const long long tiles = m_tiles * (n_total / bn);
-        const double t = (double)ceil_div(tiles, kNumSMs) * std::max(k_steps * mma, epi) + 0.02 * k_steps * mma * (n_total / bn);   // tie-break: fewer A re-reads
+        const double t = (double)ceil_div(tiles, kNumSMs) * (std::max(k_steps * mma, epi) + ovh) + 0.02 * k_steps * mma * (n_total / bn);   // tie-break: fewer A re-reads
         if (t < best) { best = t; best_bn = bn; }
     }
     return best_bn;
 }
+// Tiny levels (4x4 / 8x8 images: several images per 128-pixel tile).  Measured with clock stamps inside conv_tc_kernel
+// (TS2D_TC_DBG, profiles/r01g_tiny_levels.txt): (1) the epilogue's per-value double atomics (a tile spans several images, so the
+// per-thread statistics accumulators cannot be used) cost 20-46 k cycles per launch; (2) the main loop takes ~34 k cycles whether the
+// 72 k-chunks of an output tile run on 1, 3 or 9 CTAs: all CTAs that share an activation tile read the same L2 lines, and those
+// (1 KB apart) live in a handful of L2 slices.  So splitting K buys nothing, removing the atomics does: the "partial" mode stores the
+// fp32 accumulators and splitk_finish_kernel takes the statistics and normalises (one launch instead of norm_act_kernel).
+// TS2D_KSPLIT: unset / 1 = partial mode without a split, 0 = epilogue atomics + norm_act_kernel, 3 / 9 = split K over tap groups.
+constexpr int kSplitMaxHW = 256;
+static int tiny_ksplit() { return env_int("TS2D_KSPLIT", 1); }
 
+// promo: CUtensorMapL2promotion (0 none, 1 64 B, 2 128 B, 3 256 B)
 static int encode_map(CUtensorMap *tm, void *base, int rank, const cuuint64_t *dims, const cuuint64_t *strides_bytes, const cuuint32_t *box,
-                      int kc, size_t es, bool is_bf16) {
+                      int kc, size_t es, bool is_bf16, int promo = 3) {
     PFN_encodeTiled fn = get_encode_fn();
     if (!fn) { set_error("cuTensorMapEncodeTiled entry point not available"); return TS2D_ERR_DEVICE; }
     cuuint32_t estr[5] = {1, 1, 1, 1, 1};
     (void)es;
     const CUtensorMapSwizzle sw = kc == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
     CUresult r = fn(tm, is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, (cuuint32_t)rank, base, dims,
-                    strides_bytes, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    strides_bytes, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw, (CUtensorMapL2promotion)promo,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed with CUresult %d (rank %d)", (int)r, rank); return TS2D_ERR_CUDA; }
     return TS2D_OK;
@@ -170,23 +186,28 @@ static int encode_map(CUtensorMap *tm, void *base, int rank, const cuuint64_t *d
 // activation map for a conv input: stride 1 -> (C, W, H, N); stride 2 -> parity view (px*ps + C, W/2, 2, H/2, N)
 static int encode_act_map(CUtensorMap *tm, const void *base, long long ps, int Cin, int Hin, int Win, int Nmax, bool stride2, int kc, int tw, int th,
                           int tn, size_t es, bool is_bf16) {
+    // a box that takes only part of every pixel (half of a concat buffer, or every other pixel of the parity view) must not be
+    // promoted to 256-byte L2 requests: the other half is fetched from DRAM and never used (TS2D_L2PROMO_SUB, measured on enc1.0)
+    static const int promo_full = env_int("TS2D_L2PROMO", 3), promo_sub = env_int("TS2D_L2PROMO_SUB", 3);
+    const int promo = (stride2 || ps > Cin) ? promo_sub : promo_full;
     if (!stride2) {
         cuuint64_t dims[4] = {(cuuint64_t)Cin, (cuuint64_t)Win, (cuuint64_t)Hin, (cuuint64_t)Nmax};
         cuuint64_t str[3] = {(cuuint64_t)(ps * es), (cuuint64_t)(ps * es * Win), (cuuint64_t)(ps * es * Win * Hin)};
         cuuint32_t box[4] = {(cuuint32_t)kc, (cuuint32_t)tw, (cuuint32_t)th, (cuuint32_t)tn};
-        return encode_map(tm, const_cast<void *>(base), 4, dims, str, box, kc, es, is_bf16);
+        return encode_map(tm, const_cast<void *>(base), 4, dims, str, box, kc, es, is_bf16, promo);
     }
     cuuint64_t dims[5] = {(cuuint64_t)(ps + Cin), (cuuint64_t)(Win / 2), 2, (cuuint64_t)(Hin / 2), (cuuint64_t)Nmax};
     cuuint64_t str[4] = {(cuuint64_t)(2 * ps * es), (cuuint64_t)(ps * es * Win), (cuuint64_t)(2 * ps * es * Win), (cuuint64_t)(ps * es * Win * Hin)};
     cuuint32_t box[5] = {(cuuint32_t)kc, (cuuint32_t)tw, 1, (cuuint32_t)th, (cuuint32_t)tn};
-    return encode_map(tm, const_cast<void *>(base), 5, dims, str, box, kc, es, is_bf16);
+    return encode_map(tm, const_cast<void *>(base), 5, dims, str, box, kc, es, is_bf16, promo);
 }
 
 static int encode_w_map(CUtensorMap *tm, const void *base, int Cin, int Cout, int taps, int kc, int bn, size_t es, bool is_bf16) {
     cuuint64_t dims[3] = {(cuuint64_t)Cin, (cuuint64_t)Cout, (cuuint64_t)taps};
     cuuint64_t str[2] = {(cuuint64_t)(Cin * es), (cuuint64_t)(Cin * es * Cout)};
     cuuint32_t box[3] = {(cuuint32_t)kc, (cuuint32_t)bn, 1};
-    return encode_map(tm, const_cast<void *>(base), 3, dims, str, box, kc, es, is_bf16);
+    static const int promo_w = env_int("TS2D_L2PROMO_W", 3);
+    return encode_map(tm, const_cast<void *>(base), 3, dims, str, box, kc, es, is_bf16, promo_w);
 }
 
 template <int BN, int KC, typename DT>
@@ -541,6 +562,10 @@ extern "C" int ts2d_unet_finalize(ts2d_unet *u) {
     const size_t ss_off = off; off += align((size_t)N * u->C[0] * 2 * sizeof(float));
     const size_t a_off = off; off += align(max_act);
     const size_t b_off = off; off += align(max_act);
+    size_t max_partial = 0;
+    for (auto &c : u->convs)
+        if (c.Hout * c.Wout <= kSplitMaxHW && c.kh * c.kw == 9) max_partial = std::max(max_partial, (size_t)9 * N * c.Hout * c.Wout * c.cout * sizeof(float));
+    const size_t partial_off = off; off += align(max_partial);
     const size_t stats_off = off;
     size_t sbytes = 0;
     for (auto &c : u->convs) sbytes += align((size_t)N * c.cout * 2 * sizeof(double));
@@ -553,6 +578,8 @@ extern "C" int ts2d_unet_finalize(ts2d_unet *u) {
     for (int l = 0; l < L - 1; ++l) u->cat[l] = u->arena + cat_off[l];
     u->bott = u->arena + bott_off; u->raw = u->arena + raw_off; u->rawB = u->arena + rawb_off;
     u->feat_ss = reinterpret_cast<float *>(u->arena + ss_off); u->tmpA = u->arena + a_off; u->tmpB = u->arena + b_off;
+    u->partial = max_partial ? reinterpret_cast<float *>(u->arena + partial_off) : nullptr;
+    u->partial_bytes = max_partial;
     u->stats_arena = reinterpret_cast<double *>(u->arena + stats_off);
     u->stats_bytes = sbytes;
     size_t so = 0;
@@ -675,6 +702,20 @@ static int prof_end(ts2d_unet *u, const std::string &name, int kind, double flop
     return TS2D_OK;
 }
 
+template <typename T>
+static int launch_splitk_finish(int S, dim3 grid, const float *partial, const float *bias, const float *gamma, const float *beta, void *out, long long out_ps,
+                                int HW, int C, long long mtot, float eps, float slope, cudaStream_t st) {
+#define TS2D_SKF(SS, JJ) splitk_finish_kernel<T, SS, JJ><<<grid, 256, 0, st>>>(partial, bias, gamma, beta, (T *)out, out_ps, HW, C, mtot, eps, slope)
+    const int J = HW <= 16 ? 2 : HW <= 64 ? 8 : 32;
+    if (S == 1) { if (J == 2) TS2D_SKF(1, 2); else if (J == 8) TS2D_SKF(1, 8); else TS2D_SKF(1, 32); }
+    else if (S == 3) { if (J == 2) TS2D_SKF(3, 2); else if (J == 8) TS2D_SKF(3, 8); else TS2D_SKF(3, 32); }
+    else if (S == 9) { if (J == 2) TS2D_SKF(9, 2); else if (J == 8) TS2D_SKF(9, 8); else TS2D_SKF(9, 32); }
+    else { set_error("splitk_finish_kernel: unsupported slice count %d", S); return TS2D_ERR_UNSUPPORTED; }
+#undef TS2D_SKF
+    TS2D_LAUNCH_CHECK();
+    return TS2D_OK;
+}
+
 static int run_norm(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st);
 
 static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
@@ -713,11 +754,21 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
         int tw, th, tn;
         choose_tile(c.Hout, c.Wout, N, tw, th, tn);
         const long long m_tiles = (long long)ceil_div(c.Wout, tw) * ceil_div(c.Hout, th) * ceil_div(N, tn);
-        const int bn = choose_bn(c.cout, m_tiles, c.kh * c.kw * c.cin / 16);
+        int bn = choose_bn(c.cout, m_tiles, c.kh * c.kw * c.cin / 16), ksplit = 0;       // ksplit >= 1: partial mode
+        const long long mtot = (long long)N * c.Hout * c.Wout;
+        if (tn > 1 && c.Hout * c.Wout <= kSplitMaxHW && c.kh * c.kw == 9 && !c.defer && u->partial) {
+            const int S = tiny_ksplit();
+            if ((S == 1 || S == 3 || S == 9) && (size_t)S * mtot * c.cout * sizeof(float) <= u->partial_bytes) {
+                ksplit = S;
+                const int fbn = env_int("TS2D_KSPLIT_BN", 0);
+                bn = (fbn && c.cout % fbn == 0) ? fbn : choose_bn(c.cout, m_tiles * S, c.kh * c.kw * c.cin / 16 / S);
+            }
+        }
         fill_tc_params(p, N, c.Hout, c.Wout, c.cout, c.cin, c.kc, bn, c.kh * c.kw, c.kw, (c.kh - 1) / 2, (c.kw - 1) / 2, s2, c.in_ps);
         p.tw = tw; p.th = th; p.tn = tn;
         p.tiles_w = ceil_div(c.Wout, tw); p.tiles_h = ceil_div(c.Hout, th); p.tiles_n = ceil_div(N, tn);
         p.out_ps = c.cout; p.out = c.out_raw; p.bias = c.b.dev; p.stats = c.stats;
+        if (ksplit >= 1) { p.ksplit = ksplit; p.partial = u->partial; p.stats = nullptr; p.bias = nullptr; }
         // descriptors depend on (input pointer, batch-dependent tile box, BN): cache by (N, bn)
         if (c.first || c.bn != bn || c.enc_n != N) {
             if ((rc = encode_act_map(&c.tmA, c.in, c.in_ps, c.cin, c.Hin, c.Win, pl.max_batch, s2, c.kc, tw, th, tn, es, is_bf16))) return rc;
@@ -725,8 +776,50 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
             c.bn = bn;
             c.enc_n = N;
         }
+        static long long *tc_dbg = nullptr;
+        static const int tc_dbg_on = env_int("TS2D_TC_DBG", 0);
+        for (int rep = 1; rep < tc_dbg_on; ++rep) {      // TS2D_TC_DBG = 2: every launch twice (the second finds its weights in L2)
+            rc = is_bf16 ? launch_tc<__nv_bfloat16>(bn, c.kc, c.tmA, c.tmB, p, st) : launch_tc<__half>(bn, c.kc, c.tmA, c.tmB, p, st);
+            if (rc) return rc;
+        }
+        if (tc_dbg_on) {
+            if (!tc_dbg) TS2D_CHECK_CUDA(cudaMalloc(&tc_dbg, kNumSMs * 8 * sizeof(long long)));
+            TS2D_CHECK_CUDA(cudaMemsetAsync(tc_dbg, 0, kNumSMs * 8 * sizeof(long long), st));
+            p.dbg = tc_dbg;
+        }
         rc = is_bf16 ? launch_tc<__nv_bfloat16>(bn, c.kc, c.tmA, c.tmB, p, st) : launch_tc<__half>(bn, c.kc, c.tmA, c.tmB, p, st);
         if (rc) return rc;
+        if (tc_dbg_on) {
+            // clock stamps (cycles since the CTA started): prologue, first loads issued, all loads issued, first operands landed,
+            // all MMAs issued, epilogue done, teardown; CTA 0 and the maximum over CTAs
+            std::vector<long long> h(kNumSMs * 8);
+            TS2D_CHECK_CUDA(cudaStreamSynchronize(st));
+            TS2D_CHECK_CUDA(cudaMemcpy(h.data(), tc_dbg, h.size() * sizeof(long long), cudaMemcpyDeviceToHost));
+            const int total = (int)(m_tiles * (c.cout / bn) * std::max(1, ksplit)), g = std::min(total, kNumSMs);
+            long long mx[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+            for (int b = 0; b < g; ++b) for (int k = 0; k < 7; ++k) mx[k] = std::max(mx[k], h[b * 8 + k]);
+            fprintf(stderr, "[tc_dbg] %-7s bn %3d kc %2d split %d grid %3d chunks/tile %3d | cta0 %lld %lld %lld %lld %lld %lld %lld | max %lld %lld %lld %lld %lld %lld %lld\n",
+                    c.name.c_str(), bn, c.kc, ksplit, g, c.kh * c.kw * c.cin / c.kc / std::max(1, ksplit), h[0], h[1], h[2], h[3], h[4], h[5], h[6], mx[0], mx[1], mx[2],
+                    mx[3], mx[4], mx[5], mx[6]);
+        }
+        if (ksplit >= 1) {
+            // finish: slice sum + bias + statistics + InstanceNorm + LeakyReLU in one small launch (no norm_act pass)
+            u->launches++;
+            const double px = (double)mtot;
+            if ((rc = prof_end(u, c.name, 0, 2.0 * px * c.kh * c.kw * c.cin * c.cout, ((double)N * c.Hin * c.Win * c.cin + px * c.cout) * es, st))) return rc;
+            if ((rc = prof_begin(u, st))) return rc;
+            const dim3 grid(c.cout / 32, N);
+            const int HW = c.Hout * c.Wout;
+            rc = is_bf16 ? launch_splitk_finish<__nv_bfloat16>(ksplit, grid, u->partial, c.b.dev, c.gamma.dev, c.beta.dev, c.norm_out, c.out_ps, HW, c.cout, mtot,
+                                                               pl.eps, pl.negative_slope, st)
+                         : launch_splitk_finish<__half>(ksplit, grid, u->partial, c.b.dev, c.gamma.dev, c.beta.dev, c.norm_out, c.out_ps, HW, c.cout, mtot, pl.eps,
+                                                        pl.negative_slope, st);
+            if (rc) return rc;
+            TS2D_LAUNCH_CHECK();
+            u->launches++;
+            c.materialized = true;
+            return prof_end(u, c.name + ".norm", 2, 0.0, (double)ksplit * px * c.cout * 4 + px * c.cout * es, st);
+        }
     } else if (c.first_tc) {
         FirstTcParams p;
         memset(&p, 0, sizeof(p));

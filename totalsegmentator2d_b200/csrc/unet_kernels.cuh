@@ -304,6 +304,65 @@ __global__ void __launch_bounds__(256) norm_finalize_kernel(const double *stats,
 }
 
 // ------------------------------------------------------------------------------------------------------
+// Tiny levels (H*W <= 256 per image): finish of a split-K convolution.  conv_tc_kernel left `ksplit` fp32 partial sums per
+// output value; one block per (32-channel block, image) adds them in slice order (deterministic), adds the bias, takes the
+// InstanceNorm statistics of the fp32 values, rounds to the storage type (what the unsplit epilogue stores as "raw") and
+// applies normalisation + LeakyReLU with the arithmetic of norm_act_kernel.  Replaces epilogue statistics + norm_act_kernel.
+// lane = channel, warp w takes pixels w, w + 8, ...   partial: [ksplit][N*HW][C] fp32;  out: [N][HW] pixels, stride out_ps.
+// ------------------------------------------------------------------------------------------------------
+// S = slices, J = pixels per thread (H*W <= 8*J); everything unrolled so that the S*J loads of a thread are independent and in flight together
+template <typename T, int S, int J>
+__global__ void __launch_bounds__(256, 1) splitk_finish_kernel(const float *partial, const float *bias, const float *gamma, const float *beta, T *out,
+                                                               long long out_ps, int HW, int C, long long mtot, float eps, float slope) {
+    __shared__ float s_red[2][8][32];
+    __shared__ float s_ss[2][32];
+    const int n = blockIdx.y, lane = threadIdx.x & 31, w = threadIdx.x >> 5, c = blockIdx.x * 32 + lane;
+    const float b = bias ? bias[c] : 0.f;
+    const float *base = partial + (long long)n * HW * C + c;
+    const long long slice = mtot * C;
+    float v[J];
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+        const int pix = min(w + 8 * j, HW - 1);            // clamped: no branch between the loads
+        const float *src = base + (long long)pix * C;
+        float a = src[0];
+#pragma unroll
+        for (int ks = 1; ks < S; ++ks) a += src[ks * slice];
+        v[j] = a + b;
+    }
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int j = 0; j < J; ++j)
+        if (w + 8 * j < HW) { s1 += v[j]; s2 = fmaf(v[j], v[j], s2); }
+    s_red[0][w][lane] = s1;
+    s_red[1][w][lane] = s2;
+    __syncthreads();
+    if (w == 0) {
+        double t1 = 0.0, t2 = 0.0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { t1 += (double)s_red[0][k][lane]; t2 += (double)s_red[1][k][lane]; }
+        const double mean = t1 / (double)HW;
+        const double var = fmax(t2 / (double)HW - mean * mean, 0.0);
+        const double rstd = 1.0 / sqrt(var + (double)eps);
+        const float g = gamma ? gamma[c] : 1.f, be = beta ? beta[c] : 0.f;
+        s_ss[0][lane] = (float)(rstd * (double)g);
+        s_ss[1][lane] = (float)((double)be - mean * rstd * (double)g);
+    }
+    __syncthreads();
+    const float sc = s_ss[0][lane], sh = s_ss[1][lane];
+    T *dst = out + ((long long)n * HW) * out_ps + c;
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+        const int pix = w + 8 * j;
+        if (pix < HW) {
+            float y = fmaf(to_f32<T>(from_f32<T>(v[j])), sc, sh);
+            y = y > 0.f ? y : y * slope;
+            dst[(long long)pix * out_ps] = from_f32<T>(y);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
 // Fused: mirror-TTA average + Gaussian-weighted tile blend + 1x1 segmentation head + (logits | threshold+paste).
 // The head is linear, so  sum_t g_t (W f_t + b) / sum_t g_t  ==  W (sum_t g_t f_t / sum_t g_t) + b : the F-channel
 // decoder features are blended and the head applied once per output pixel.  One thread per output pixel.
