@@ -336,13 +336,21 @@ def run_b200(args):
     l0 = launches_now()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
+    th0 = time.perf_counter()
     for _ in range(args.steps):
         step_device()
+    host_loop_ms = 1000.0 * (time.perf_counter() - th0) / (S * args.steps)         # includes waiting on the full launch queue
     e1.record()
     torch.cuda.synchronize()
     ms_local = e0.elapsed_time(e1)
-    barrier(world)
     launches = launches_now() - l0
+    # host time to issue ONE study's launches into an empty queue (no sync inside): the device time above is not a host artefact
+    th0 = time.perf_counter()
+    ts.predict_volume_device(dev_vols[0], SPACING, None, mask=masks[0], present=presents[0])
+    _ops.merge_present_order(masks[0], presents[0], offs, out=merged[0])
+    host_enqueue_ms = 1000.0 * (time.perf_counter() - th0)
+    torch.cuda.synchronize()
+    barrier(world)
     clocks = sampler.stop() if rank == 0 else None
     ms_total = max_over_ranks(ms_local, world)
     studies_total = S * args.steps * world
@@ -446,7 +454,7 @@ def run_b200(args):
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
                 "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": args.precision, "data": "synthetic", "config": config_dict(args, shape, patch, S),
-                "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+                "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "host_enqueue_ms_per_study": host_enqueue_ms,
                 "roofline": {"bound": "tensor", "kernel": "conv_tc_kernel (tcgen05 implicit-GEMM conv, all conv/transposed-conv launches of one study)",
                              "achieved": conv_tflops, "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
                              "frac": conv_tflops / peaks["bf16_tflops_sustained"], "traffic": conv_traffic,

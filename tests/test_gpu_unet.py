@@ -189,3 +189,18 @@ def test_partial_mode_tiny_levels(precision, tol, monkeypatch):
     p, sd, spec = _make([32, 64, 128, 256, 256], (64, 64), heads=7, precision=precision, seed=5)
     again = p.predict_tile_logits(xd).cpu()
     assert torch.equal(again, outs["9"][1])
+
+
+@pytest.mark.parametrize("precision", ["bf16", "fp16"])
+def test_multicast_pairs_bit_identical(precision, monkeypatch):
+    """conv_tc_kernel as clusters of two CTAs (TS2D_MC=1: each CTA loads half of the weight tile, TMA multicast into both shared
+    memories, tcgen05.commit multicast frees the slot for both producers) computes exactly what the single-CTA kernel computes."""
+    dt = torch.bfloat16 if precision == "bf16" else torch.float16
+    outs = []
+    for mc in ("0", "1"):
+        monkeypatch.setenv("TS2D_MC", mc)
+        p, sd, spec = _make([32, 64, 128, 256], (64, 96), heads=6, precision=precision, seed=13)
+        x, xd = _tiles(4, 2, (64, 96), 6, dt)
+        outs.append((p.predict_tile_logits(xd).cpu(), p.forward_debug(xd, "dec0.0", (128, 16, 24)).cpu()))
+        p.close()
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])

@@ -70,6 +70,15 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
+// ---- programmatic dependent launch (PDL) ----
+// The U-Net is ~75 back-to-back launches of 10-150 us on one stream.  Kernels launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization may become resident while their predecessor drains (its CTAs that finished early,
+// the 2-vs-3 tile imbalance of the persistent grids): launch latency, barrier init, TMEM allocation and the tensor-map fetch overlap the
+// predecessor's tail.  griddep_wait() returns once every prerequisite grid has completed and its writes are visible; nothing a
+// predecessor writes (or still reads) may be touched before it.  Both are no-ops for a normally launched kernel.
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // 16-byte streaming load (read once: do not allocate in L1)
 __device__ __forceinline__ uint4 ld_stream_16(const void *p) {
     uint4 v;

@@ -71,6 +71,8 @@ __global__ void __launch_bounds__(kFtcThreads, 2) conv_first_tc_kernel(const Fir
     __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
+    griddep_launch_dependents();
+    griddep_wait();          // the weights / bias above are constants; the tiles and the output buffer belong to earlier launches
 
     const int tiles_per_img = p.tiles_x * p.tiles_y;
     const int total_tiles = tiles_per_img * p.N;

@@ -121,6 +121,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
+    griddep_launch_dependents();
+    if (!(warp == 0 && lane == 0)) griddep_wait();      // (the producer thread first issues the weight loads: constants, see below)
 
     const int tiles_per_img = p.tiles_x * p.tiles_y;
     const int total_tiles = tiles_per_img * p.N;
@@ -138,6 +140,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             for (int cc = 0; cc < p.cin_chunks; ++cc)
                 for (int tap = 0; tap < 9; ++tap)
                     tma_load_3d(smem_w + (cc * 9 + tap) * kWBlock, &tmB, w_bar, cc * KC, nt * BN, tap);
+            griddep_wait();                             // the resident weights stream in while the previous launch drains
             int stage = 0;
             uint32_t phase = 0;
             for (int tile = t_begin; tile < t_end; ++tile) {

@@ -52,6 +52,10 @@ struct ConvTcParams {
     int ksplit;                  // 0 / 1: off
     float *partial;
     long long *dbg;              // TS2D_TC_DBG: per-CTA clock stamps (8 per CTA), see run_conv
+    // mc = 1: launched as clusters of 2 CTAs that walk neighbouring M tiles of the same channel block in lock step; each CTA loads its own
+    // activation tile and HALF of the weight tile, multicast into both CTAs' shared memory.  The TMA unit issues one request per 64/128-byte
+    // box row (~1.7 cycles each, measured): 128 + BN/2 rows per k-chunk instead of 128 + BN.  (tmB box = BN/2 rows.)
+    int mc;
 };
 constexpr int kTcThreads = 384;
 
@@ -89,6 +93,14 @@ __device__ __forceinline__ void tma_load_5d(void *dst, const CUtensorMap *tm, ui
     asm volatile("cp.async.bulk.tensor.5d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
                  ::"r"(smem_u32(dst)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4) : "memory");
 }
+__device__ __forceinline__ void tma_load_3d_mc(void *dst, const CUtensorMap *tm, uint64_t *bar, int c0, int c1, int c2, uint16_t mask) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4, %5}], [%2], %6;"
+                 ::"r"(smem_u32(dst)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
 __device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcgen05_commit(uint64_t *bar) {
@@ -133,6 +145,15 @@ __device__ __forceinline__ void tcgen05_commit_pred(uint32_t leader, uint64_t *b
         "setp.ne.b32 q, %0, 0;\n"
         "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%1];\n"
         "}\n" ::"r"(leader), "r"(smem_u32(bar)) : "memory");
+}
+// same, arriving on the barrier at this offset in every CTA of `mask` (frees the slot for both producers of a multicast pair)
+__device__ __forceinline__ void tcgen05_commit_mc_pred(uint32_t leader, uint64_t *bar, uint16_t mask) {
+    asm volatile(
+        "{\n"
+        ".reg .pred q;\n"
+        "setp.ne.b32 q, %0, 0;\n"
+        "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%1], %2;\n"
+        "}\n" ::"r"(leader), "r"(smem_u32(bar)), "h"(mask) : "memory");
 }
 template <int KC> __device__ __forceinline__ uint32_t desc_lo(uint32_t saddr) { return ((saddr >> 4) & 0x3FFFu) | (1u << 16); }
 template <int KC> __device__ __forceinline__ constexpr uint32_t desc_hi(uint32_t sbo_bytes) {
@@ -300,7 +321,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
-        for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], p.mc ? 2 : 1); }      // mc: both CTAs' MMAs free a slot
         for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], kAlt ? 128 : 256); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -311,17 +332,25 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     tcgen05_fence_before();
     __syncthreads();
     tcgen05_fence_after();
+    if (p.mc) cluster_sync_all();                   // the peer's barriers exist before anything is multicast to them
+    const uint32_t rank = p.mc ? cluster_ctarank() : 0u;
     const uint32_t tmem_base = *tmem_ptr;
-    if (dbg && threadIdx.x == 0) dbg[0] = clock64() - t_start;          // prologue (barriers, TMEM allocation)
+    griddep_launch_dependents();
+    griddep_wait();                                                     // activations / statistics of the previous launches are complete
+    if (dbg && threadIdx.x == 0) dbg[0] = clock64() - t_start;          // prologue (barriers, TMEM allocation) + wait for the predecessor
 
     const int m_tiles = p.tiles_n * p.tiles_h * p.tiles_w;
     const int ksplit = p.ksplit > 1 ? p.ksplit : 1;
-    const int total_tiles = m_tiles * p.n_tiles_n * ksplit;
+    // the tile sequence is walked in units of `mstep` M tiles (mc: a pair of CTAs takes M tiles 2j and 2j + 1; m_tiles is even then)
+    const int mstep = p.mc ? 2 : 1;
+    const int mseq = m_tiles / mstep;
+    const int total_tiles = mseq * p.n_tiles_n * ksplit;
     const int k_chunks = p.taps * p.cin_chunks;
     const int k_per = k_chunks / ksplit;          // k-chunks per tile (the host guarantees divisibility)
-    // tile t -> channel block nt = t / m_tiles (slowest), m tile = t % m_tiles = (image group, y tile, x tile) with x fastest
-    const int t_begin = (int)((long long)total_tiles * blockIdx.x / gridDim.x);
-    const int t_end = (int)((long long)total_tiles * (blockIdx.x + 1) / gridDim.x);
+    // tile t -> channel block nt = t / mseq (slowest), m tile = (t % mseq) * mstep + rank = (image group, y tile, x tile) with x fastest
+    const int nparts = gridDim.x / mstep, part = blockIdx.x / mstep;
+    const int t_begin = (int)((long long)total_tiles * part / nparts);
+    const int t_end = (int)((long long)total_tiles * (part + 1) / nparts);
 
     if (warp == 0) {
         // ===================== TMA producer =====================
@@ -330,7 +359,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             uint32_t phase = 0;
             for (int tile = t_begin; tile < t_end; ++tile) {
                 const int ot = tile / ksplit, ks = tile - ot * ksplit;      // (output tile, K slice), slice fastest
-                const int nt = ot / m_tiles, mt = ot - nt * m_tiles;
+                const int nt = ot / mseq, mt = (ot - nt * mseq) * mstep + (int)rank;
                 const int xt = mt % p.tiles_w, yt = (mt / p.tiles_w) % p.tiles_h, nn = mt / (p.tiles_w * p.tiles_h);
                 const int x0 = xt * p.tw, y0 = yt * p.th, n0 = nn * p.tn;
                 for (int kc = ks * k_per; kc < (ks + 1) * k_per; ++kc) {
@@ -349,7 +378,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         const int hoff = (dr - py) / 2, woff = (ds - px) / 2;
                         tma_load_5d(sa, &tmA, &full_bar[stage], px * p.in_ps + cc * KC, x0 + woff, py, y0 + hoff, n0);
                     }
-                    tma_load_3d(sb, &tmB, &full_bar[stage], cc * KC, nt * BN, tap);
+                    if (p.mc) tma_load_3d_mc(sb + rank * (BN / 2 * KC * 2), &tmB, &full_bar[stage], cc * KC, nt * BN + (int)rank * (BN / 2), tap, (uint16_t)3);
+                    else tma_load_3d(sb, &tmB, &full_bar[stage], cc * KC, nt * BN, tap);
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                     if (dbg && tile == t_begin && kc == ks * k_per) dbg[1] = clock64() - t_start;     // first loads issued
                 }
@@ -380,7 +410,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
                 for (int k = 0; k < KC / 16; ++k)   // 16 elements = 32 bytes along K inside the swizzled row: +2 in the (addr >> 4) field
                     tcgen05_mma_f16_lohi(leader, d_tmem, a_lo + (uint32_t)(k * 2), hi, b_lo + (uint32_t)(k * 2), hi, idesc, k ? 1u : (uint32_t)(kc != 0));
-                tcgen05_commit_pred(leader, &empty_bar[stage]);       // frees the smem slot once these MMAs retire
+                if (p.mc) tcgen05_commit_mc_pred(leader, &empty_bar[stage], (uint16_t)3);
+                else tcgen05_commit_pred(leader, &empty_bar[stage]);       // frees the smem slot once these MMAs retire
                 if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
             tcgen05_commit_pred(leader, &tmem_full[buf]);             // accumulator complete
@@ -416,10 +447,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         // tile walker (no divisions in the loop): this group's tiles are t_begin + e, e += estep
         const int estep = kAlt ? 2 : 1;
         int tile = t_begin + (kAlt ? grp : 0);
-        int nt = tile / m_tiles;
+        int nt = tile / mseq;                   // (partial mode decodes its own tiles below)
         int xt, yt, nn;
         {
-            const int mt = tile - nt * m_tiles;
+            const int mt = (tile - nt * mseq) * mstep + (int)rank;
             xt = mt % p.tiles_w; yt = (mt / p.tiles_w) % p.tiles_h; nn = mt / (p.tiles_w * p.tiles_h);
         }
         if (p.partial) {
@@ -522,7 +553,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     }
                 }
             }
-            xt += estep;
+            xt += estep * mstep;
             while (xt >= p.tiles_w) {
                 xt -= p.tiles_w;
                 if (++yt == p.tiles_h) { yt = 0; if (++nn == p.tiles_n) { nn = 0; ++nt; } }
@@ -533,6 +564,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     tcgen05_fence_before();
     __syncthreads();
+    if (p.mc) cluster_sync_all();                   // the peer may still multicast into this CTA's shared memory / arrive on its barriers
     if (dbg && threadIdx.x == 0) dbg[6] = clock64() - t_start;
     if (warp == 1) {
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kTmemCols) : "memory");

@@ -142,6 +142,33 @@ static void choose_tile(int Hout, int Wout, int N, int &tw, int &th, int &tn) {
 // an M=128, K=16 tcgen05.mma costs ~45 / 51 / 67 / 131 cycles at N = 32 / 64 / 128 / 256; an epilogue warp needs
 // ~400 cycles per 32-column chunk): time = waves x max(MMA time, epilogue time) per tile.
 static int env_int(const char *name, int dflt) { const char *v = getenv(name); return v ? atoi(v) : dflt; }
+// launch with programmatic stream serialisation (see common.cuh: every kernel launched through here calls griddep_wait() before it
+// touches anything an earlier launch produces).  TS2D_PDL=0 falls back to plain stream order.
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_pdl_cluster(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, int cluster_x, Args &&...args) {
+    static const int pdl = env_int("TS2D_PDL", 1);
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (pdl) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+    }
+    if (cluster_x > 1) {
+        attr[na].id = cudaLaunchAttributeClusterDimension;
+        attr[na].val.clusterDim.x = (unsigned)cluster_x; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = 1;
+        ++na;
+    }
+    cfg.attrs = attr; cfg.numAttrs = na;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(std::forward<Args>(args))...);
+}
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args &&...args) {
+    return launch_pdl_cluster(kern, grid, block, smem, st, 1, std::forward<Args>(args)...);
+}
 // + kTileOvh cycles per tile (TMA latency of the first chunk, tmem_full / tmem_empty round trips): decides the 1-chunk tiles of the
 // full-resolution transposed conv (BN = 32: 0.125 ms, BN = 128: one pass over A).
 static int choose_bn(int n_total, long long m_tiles, int k_steps) {
@@ -158,15 +185,16 @@ static int choose_bn(int n_total, long long m_tiles, int k_steps) {
     }
     return best_bn;
 }
-// Tiny levels (4x4 / 8x8 images: several images per 128-pixel tile).  Measured with clock stamps inside conv_tc_kernel
-// (TS2D_TC_DBG, profiles/r01g_tiny_levels.txt): (1) the epilogue's per-value double atomics (a tile spans several images, so the
-// per-thread statistics accumulators cannot be used) cost 20-46 k cycles per launch; (2) the main loop takes ~34 k cycles whether the
-// 72 k-chunks of an output tile run on 1, 3 or 9 CTAs: all CTAs that share an activation tile read the same L2 lines, and those
-// (1 KB apart) live in a handful of L2 slices.  So splitting K buys nothing, removing the atomics does: the "partial" mode stores the
-// fp32 accumulators and splitk_finish_kernel takes the statistics and normalises (one launch instead of norm_act_kernel).
-// TS2D_KSPLIT: unset / 1 = partial mode without a split, 0 = epilogue atomics + norm_act_kernel, 3 / 9 = split K over tap groups.
+// Tiny levels (H*W <= 256 per image).  Measured with clock stamps inside conv_tc_kernel (TS2D_TC_DBG,
+// profiles/r01g_tiny_levels_clock_stamps.txt): (1) on the 4x4 / 8x8 levels a 128-pixel tile spans several images, the per-thread
+// statistics accumulators cannot be used, and the epilogue's per-value double atomics cost 20-46 k cycles per launch; (2) a tile is a
+// chain of 72-144 k-chunks at ~460 cycles each on 16-96 CTAs.  "Partial" mode: K is split over `ksplit` tap groups on separate CTAs,
+// the epilogue stores fp32 accumulators, and splitk_finish_kernel adds the slices in a fixed order, takes the statistics and normalises
+// (one launch instead of norm_act_kernel).  enc6.0: 51.7 -> 14.8 us, enc7.0: 35.2 -> 12.7 us, dec0.0: 67.6 -> 19.0 us.
+// TS2D_KSPLIT (4x4 / 8x8 levels; default 9) and TS2D_KSPLIT16 (16x16 level, one image per tile; default 3):
+// 0 = epilogue statistics + norm_act_kernel, 1 = partial mode without a split, 3 / 9 = split over tap rows / taps.
 constexpr int kSplitMaxHW = 256;
-static int tiny_ksplit() { return env_int("TS2D_KSPLIT", 1); }
+static int tiny_ksplit() { return env_int("TS2D_KSPLIT", 9); }
 
 // promo: CUtensorMapL2promotion (0 none, 1 64 B, 2 128 B, 3 256 B)
 static int encode_map(CUtensorMap *tm, void *base, int rank, const cuuint64_t *dims, const cuuint64_t *strides_bytes, const cuuint32_t *box,
@@ -219,9 +247,27 @@ static int launch_tc_inst(const CUtensorMap &tmA, const CUtensorMap &tmB, const 
         attr_set = true;
     }
     const int m_tiles = p.tiles_n * p.tiles_h * p.tiles_w;
-    const int total = m_tiles * p.n_tiles_n;
+    const int total = m_tiles * p.n_tiles_n * std::max(1, p.ksplit);
+    if (p.mc) {
+        // pairs of CTAs (clusters of 2) over pairs of M tiles
+        static int max_clusters = -1;
+        if (max_clusters < 0) {
+            cudaLaunchConfig_t cfg;
+            memset(&cfg, 0, sizeof(cfg));
+            cfg.gridDim = dim3(kNumSMs & ~1); cfg.blockDim = dim3(kTcThreads); cfg.dynamicSmemBytes = smem;
+            cudaLaunchAttribute a;
+            a.id = cudaLaunchAttributeClusterDimension; a.val.clusterDim.x = 2; a.val.clusterDim.y = 1; a.val.clusterDim.z = 1;
+            cfg.attrs = &a; cfg.numAttrs = 1;
+            int n = 0;
+            if (cudaOccupancyMaxActiveClusters(&n, conv_tc_kernel<BN, KC, DT>, &cfg) != cudaSuccess || n < 1) { cudaGetLastError(); n = kNumSMs / 2; }
+            max_clusters = std::min(n, kNumSMs / 2);
+        }
+        const int pairs = std::max(1, std::min(total / 2, max_clusters));
+        TS2D_CHECK_CUDA(launch_pdl_cluster(conv_tc_kernel<BN, KC, DT>, dim3(2 * pairs), dim3(kTcThreads), smem, st, 2, tmA, tmB, p));
+        return TS2D_OK;
+    }
     const int gx = std::max(1, std::min(total, kNumSMs));
-    conv_tc_kernel<BN, KC, DT><<<gx, kTcThreads, smem, st>>>(tmA, tmB, p);
+    TS2D_CHECK_CUDA(launch_pdl(conv_tc_kernel<BN, KC, DT>, dim3(gx), dim3(kTcThreads), smem, st, tmA, tmB, p));
     TS2D_LAUNCH_CHECK();
     return TS2D_OK;
 }
@@ -252,7 +298,7 @@ static int launch_halo_inst(const CUtensorMap &tmA, const CUtensorMap &tmB, cons
     const int n_tiles_n = p.Cout / BN;
     const int total = p.tiles_x * p.tiles_y * p.N;
     const int gx = std::max(1, std::min(total, kNumSMs / n_tiles_n));
-    conv_halo_kernel<BN, KC, DT, FUSE><<<dim3(gx, n_tiles_n), kHaloThreads, smem, st>>>(tmA, tmB, p);
+    TS2D_CHECK_CUDA(launch_pdl(conv_halo_kernel<BN, KC, DT, FUSE>, dim3(gx, n_tiles_n), dim3(kHaloThreads), smem, st, tmA, tmB, p));
     TS2D_LAUNCH_CHECK();
     return TS2D_OK;
 }
@@ -320,7 +366,7 @@ static int launch_first_tc(const FirstTcParams &p, cudaStream_t st) {
     }
     const long long total = (long long)p.tiles_x * p.tiles_y * p.N;
     const int gx = (int)std::max(1LL, std::min(total / 2, (long long)kNumSMs * 2));
-    conv_first_tc_kernel<DT><<<dim3(gx, p.Cout / 32), kFtcThreads, kFtcSmemBytes, st>>>(p);
+    TS2D_CHECK_CUDA(launch_pdl(conv_first_tc_kernel<DT>, dim3(gx, p.Cout / 32), dim3(kFtcThreads), kFtcSmemBytes, st, p));
     TS2D_LAUNCH_CHECK();
     return TS2D_OK;
 }
@@ -347,7 +393,7 @@ static int launch_norm(const void *raw, const double *stats, const float *g, con
     // <= 4 blocks per SM in total: the whole grid is resident at once (no second partial wave)
     int ppb = std::max(32, ceil_div(HW, std::max(1, (kNumSMs * 4) / std::max(1, N))));
     dim3 grid(ceil_div(HW, ppb), N);
-    norm_act_kernel<T><<<grid, 256, 2 * C * sizeof(float), st>>>((const T *)raw, stats, g, b, (T *)out, out_ps, HW, C, eps, slope, ppb);
+    TS2D_CHECK_CUDA(launch_pdl(norm_act_kernel<T>, grid, dim3(256), 2 * C * sizeof(float), st, (const T *)raw, stats, g, b, (T *)out, out_ps, HW, C, eps, slope, ppb));
     TS2D_LAUNCH_CHECK();
     return TS2D_OK;
 }
@@ -705,7 +751,7 @@ static int prof_end(ts2d_unet *u, const std::string &name, int kind, double flop
 template <typename T>
 static int launch_splitk_finish(int S, dim3 grid, const float *partial, const float *bias, const float *gamma, const float *beta, void *out, long long out_ps,
                                 int HW, int C, long long mtot, float eps, float slope, cudaStream_t st) {
-#define TS2D_SKF(SS, JJ) splitk_finish_kernel<T, SS, JJ><<<grid, 256, 0, st>>>(partial, bias, gamma, beta, (T *)out, out_ps, HW, C, mtot, eps, slope)
+#define TS2D_SKF(SS, JJ) TS2D_CHECK_CUDA(launch_pdl(splitk_finish_kernel<T, SS, JJ>, grid, dim3(256), 0, st, partial, bias, gamma, beta, (T *)out, out_ps, HW, C, mtot, eps, slope))
     const int J = HW <= 16 ? 2 : HW <= 64 ? 8 : 32;
     if (S == 1) { if (J == 2) TS2D_SKF(1, 2); else if (J == 8) TS2D_SKF(1, 8); else TS2D_SKF(1, 32); }
     else if (S == 3) { if (J == 2) TS2D_SKF(3, 2); else if (J == 8) TS2D_SKF(3, 8); else TS2D_SKF(3, 32); }
@@ -756,8 +802,8 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
         const long long m_tiles = (long long)ceil_div(c.Wout, tw) * ceil_div(c.Hout, th) * ceil_div(N, tn);
         int bn = choose_bn(c.cout, m_tiles, c.kh * c.kw * c.cin / 16), ksplit = 0;       // ksplit >= 1: partial mode
         const long long mtot = (long long)N * c.Hout * c.Wout;
-        if (tn > 1 && c.Hout * c.Wout <= kSplitMaxHW && c.kh * c.kw == 9 && !c.defer && u->partial) {
-            const int S = tiny_ksplit();
+        if (c.Hout * c.Wout <= kSplitMaxHW && c.kh * c.kw == 9 && !c.defer && u->partial) {
+            const int S = tn > 1 ? tiny_ksplit() : env_int("TS2D_KSPLIT16", 3);        // 16x16 level (one image per tile): 96 CTAs x 72 chunks -> 144 x 24
             if ((S == 1 || S == 3 || S == 9) && (size_t)S * mtot * c.cout * sizeof(float) <= u->partial_bytes) {
                 ksplit = S;
                 const int fbn = env_int("TS2D_KSPLIT_BN", 0);
@@ -769,11 +815,13 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
         p.tiles_w = ceil_div(c.Wout, tw); p.tiles_h = ceil_div(c.Hout, th); p.tiles_n = ceil_div(N, tn);
         p.out_ps = c.cout; p.out = c.out_raw; p.bias = c.b.dev; p.stats = c.stats;
         if (ksplit >= 1) { p.ksplit = ksplit; p.partial = u->partial; p.stats = nullptr; p.bias = nullptr; }
+        const int mc_on = env_int("TS2D_MC", 0);
+        p.mc = (mc_on && ksplit == 0 && m_tiles % 2 == 0 && bn >= 32) ? 1 : 0;
         // descriptors depend on (input pointer, batch-dependent tile box, BN): cache by (N, bn)
-        if (c.first || c.bn != bn || c.enc_n != N) {
+        if (c.first || c.bn != bn * (p.mc ? -1 : 1) || c.enc_n != N) {
             if ((rc = encode_act_map(&c.tmA, c.in, c.in_ps, c.cin, c.Hin, c.Win, pl.max_batch, s2, c.kc, tw, th, tn, es, is_bf16))) return rc;
-            if ((rc = encode_w_map(&c.tmB, c.w_tc, c.cin, c.cout, c.kh * c.kw, c.kc, bn, es, is_bf16))) return rc;
-            c.bn = bn;
+            if ((rc = encode_w_map(&c.tmB, c.w_tc, c.cin, c.cout, c.kh * c.kw, c.kc, p.mc ? bn / 2 : bn, es, is_bf16))) return rc;
+            c.bn = bn * (p.mc ? -1 : 1);       // cache key: (BN, multicast or not)
             c.enc_n = N;
         }
         static long long *tc_dbg = nullptr;
@@ -795,7 +843,7 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
             std::vector<long long> h(kNumSMs * 8);
             TS2D_CHECK_CUDA(cudaStreamSynchronize(st));
             TS2D_CHECK_CUDA(cudaMemcpy(h.data(), tc_dbg, h.size() * sizeof(long long), cudaMemcpyDeviceToHost));
-            const int total = (int)(m_tiles * (c.cout / bn) * std::max(1, ksplit)), g = std::min(total, kNumSMs);
+            const int total = (int)(m_tiles * (c.cout / bn) * std::max(1, ksplit)), g = std::min(total, kNumSMs) & (p.mc ? ~1 : ~0);
             long long mx[8] = {0, 0, 0, 0, 0, 0, 0, 0};
             for (int b = 0; b < g; ++b) for (int k = 0; k < 7; ++k) mx[k] = std::max(mx[k], h[b * 8 + k]);
             fprintf(stderr, "[tc_dbg] %-7s bn %3d kc %2d split %d grid %3d chunks/tile %3d | cta0 %lld %lld %lld %lld %lld %lld %lld | max %lld %lld %lld %lld %lld %lld %lld\n",
@@ -891,10 +939,12 @@ static int run_up(ts2d_unet *u, UpLayer &up, int N, cudaStream_t st) {
         p.tiles_w = ceil_div(up.Win, tw); p.tiles_h = ceil_div(up.Hin, th); p.tiles_n = ceil_div(N, tn);
         p.my = up.sh; p.mx = up.sw; p.Hfull = up.Hin * up.sh; p.Wfull = up.Win * up.sw;
         p.out_ps = up.out_ps; p.out = up.out; p.bias = up.b.dev; p.stats = nullptr;
-        if (up.bn != bn || up.enc_n != N) {
+        const int mc_on = env_int("TS2D_MC", 0);
+        p.mc = (mc_on && m_tiles % 2 == 0) ? 1 : 0;
+        if (up.bn != bn * (p.mc ? -1 : 1) || up.enc_n != N) {
             if ((rc = encode_act_map(&up.tmA, up.in, up.cin, up.cin, up.Hin, up.Win, pl.max_batch, false, up.kc, tw, th, tn, es, is_bf16))) return rc;
-            if ((rc = encode_w_map(&up.tmB, up.w_tc, up.cin, n_total, 1, up.kc, bn, es, is_bf16))) return rc;      // [tap][Cout][Cin] viewed as [taps*Cout][Cin]
-            up.bn = bn;
+            if ((rc = encode_w_map(&up.tmB, up.w_tc, up.cin, n_total, 1, up.kc, p.mc ? bn / 2 : bn, es, is_bf16))) return rc;      // [tap][Cout][Cin] viewed as [taps*Cout][Cin]
+            up.bn = bn * (p.mc ? -1 : 1);
             up.enc_n = N;
         }
         rc = is_bf16 ? launch_tc<__nv_bfloat16>(bn, up.kc, up.tmA, up.tmB, p, st) : launch_tc<__half>(bn, up.kc, up.tmA, up.tmB, p, st);

@@ -205,6 +205,8 @@ __global__ void __launch_bounds__(256) norm_act_kernel(const T *raw, const doubl
                                                        long long out_ps, int HW, int C, float eps, float slope, int pix_per_block) {
     extern __shared__ float s_ss[];    // scale[C], shift[C]
     const int n = blockIdx.y;
+    griddep_launch_dependents();
+    griddep_wait();
     for (int c = threadIdx.x; c < C; c += blockDim.x) {
         const double mean = stats[((long long)n * C + c) * 2] / (double)HW;
         const double var = fmax(stats[((long long)n * C + c) * 2 + 1] / (double)HW - mean * mean, 0.0);
@@ -243,6 +245,15 @@ __global__ void __launch_bounds__(256) norm_act_kernel(const T *raw, const doubl
                     w[k] = pack2<T>(y0, y1);
                 }
             };
+            for (; pix + 7 * pstep < p1; pix += 8 * pstep, s += 8 * s_step, d += 8 * d_step) {
+                uint4 v[8];                       // 8 independent 16-byte loads in flight per thread (the projection kernel's depth)
+#pragma unroll
+                for (int u = 0; u < 8; ++u) v[u] = ld_stream_16(s + u * s_step);
+#pragma unroll
+                for (int u = 0; u < 8; ++u) apply(v[u]);
+#pragma unroll
+                for (int u = 0; u < 8; ++u) *reinterpret_cast<uint4 *>(d + u * d_step) = v[u];
+            }
             for (; pix + 3 * pstep < p1; pix += 4 * pstep, s += 4 * s_step, d += 4 * d_step) {
                 uint4 v[4];
 #pragma unroll
@@ -318,6 +329,8 @@ __global__ void __launch_bounds__(256, 1) splitk_finish_kernel(const float *part
     __shared__ float s_ss[2][32];
     const int n = blockIdx.y, lane = threadIdx.x & 31, w = threadIdx.x >> 5, c = blockIdx.x * 32 + lane;
     const float b = bias ? bias[c] : 0.f;
+    griddep_launch_dependents();
+    griddep_wait();
     const float *base = partial + (long long)n * HW * C + c;
     const long long slice = mtot * C;
     float v[J];
