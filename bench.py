@@ -260,6 +260,17 @@ def dist_setup(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if world > 1:
+        # before any pinned allocation: keep this rank's host buffers on the socket its GPU hangs off
+        from totalsegmentator2d_b200 import shard
+        try:
+            bus = torch.cuda.get_device_properties(local).pci_bus_id
+            bdf = "{:04x}:{:02x}:{:02x}.0".format(torch.cuda.get_device_properties(local).pci_domain_id, bus,
+                                                   torch.cuda.get_device_properties(local).pci_device_id)
+        except AttributeError:
+            bdf = ""
+        cpus = shard.bind_to_gpu(local, int(os.environ.get("LOCAL_WORLD_SIZE", world)), bdf)
+        print("[bench] rank {} gpu {} ({}) bound to {} cpus{}".format(rank, local, bdf, len(cpus), " {}..{}".format(cpus[0], cpus[-1]) if cpus else ""),
+              file=sys.stderr)
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))

@@ -116,3 +116,35 @@ def test_model_owner_round_robin():
     assert shard.owned_models(5, 0, 1) == [0, 1, 2, 3, 4]
     with pytest.raises(ValueError):
         shard.model_owner(0, 2, 2)
+
+
+def test_gpu_numa_binding_helpers(tmp_path, monkeypatch):
+    """bind_to_gpu: CPUs of the GPU's NUMA node from (a fake) sysfs, an even split when sysfs is silent, off with TS2D_BIND=0"""
+    import os
+    from totalsegmentator2d_b200 import shard
+    assert shard._parse_cpulist("0-3,8,10-11\n") == [0, 1, 2, 3, 8, 10, 11]
+    dev = tmp_path / "bus/pci/devices/0000:1b:00.0"
+    dev.mkdir(parents=True)
+    (dev / "numa_node").write_text("1\n")
+    node = tmp_path / "devices/system/node/node1"
+    node.mkdir(parents=True)
+    (node / "cpulist").write_text("4-7\n")
+    assert shard.gpu_numa_cpus("0000:1B:00.0", str(tmp_path)) == [4, 5, 6, 7]
+    assert shard.gpu_numa_cpus("1b:00.0", str(tmp_path)) == [4, 5, 6, 7]
+    assert shard.gpu_numa_cpus("0000:99:00.0", str(tmp_path)) == []
+    (dev / "numa_node").write_text("-1\n")
+    assert shard.gpu_numa_cpus("0000:1b:00.0", str(tmp_path)) == []
+    if not hasattr(os, "sched_setaffinity"):
+        return
+    before = sorted(os.sched_getaffinity(0))
+    try:
+        assert shard.bind_to_gpu(0, 1) == []                                   # a single local rank is left alone
+        monkeypatch.setenv("TS2D_BIND", "0")
+        assert shard.bind_to_gpu(1, 2) == []
+        monkeypatch.delenv("TS2D_BIND")
+        if len(before) >= 2:
+            got = shard.bind_to_gpu(1, 2, "0000:1b:00.0", str(tmp_path))       # sysfs silent -> even split
+            per = len(before) // 2
+            assert got == before[per:2 * per] and sorted(os.sched_getaffinity(0)) == got
+    finally:
+        os.sched_setaffinity(0, before)

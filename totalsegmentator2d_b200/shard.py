@@ -27,6 +27,58 @@ def shard(items: Sequence[Any], rank: int, world: int) -> List[Any]:
     return [items[i] for i in shard_indices(len(items), rank, world)]
 
 
+def _parse_cpulist(text: str) -> List[int]:
+    """'0-3,8,10-11' -> [0, 1, 2, 3, 8, 10, 11]"""
+    cpus: List[int] = []
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        if "-" in part:
+            a, b = part.split("-")
+            cpus.extend(range(int(a), int(b) + 1))
+        else:
+            cpus.append(int(part))
+    return cpus
+
+
+def gpu_numa_cpus(pci_bus_id: str, sysfs: str = "/sys") -> List[int]:
+    """CPUs of the NUMA node the GPU with this PCI address ('0000:1b:00.0') hangs off; [] when sysfs does not say"""
+    try:
+        bdf = pci_bus_id.lower()
+        if len(bdf.split(":")) == 2:
+            bdf = "0000:" + bdf
+        with open(os.path.join(sysfs, "bus/pci/devices", bdf, "numa_node")) as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return []
+        with open(os.path.join(sysfs, "devices/system/node", f"node{node}", "cpulist")) as f:
+            return _parse_cpulist(f.read())
+    except (OSError, ValueError):
+        return []
+
+
+def bind_to_gpu(local_rank: int, n_local: int, pci_bus_id: str = "", sysfs: str = "/sys") -> List[int]:
+    """Pin this process (and the pinned host buffers it allocates afterwards: first touch) to the CPUs next to its GPU.
+    With 8 ranks streaming 524 MB volumes each, buffers that all sit on one socket make the other socket's GPUs pull their
+    input over the inter-socket link.  Uses the GPU's NUMA node from sysfs; when that is unknown, an even split of the
+    allowed CPUs by local rank (GPUs are enumerated socket by socket on the usual 8-GPU boards).  Returns the CPU list in
+    effect (empty = left alone).  TS2D_BIND=0 disables it."""
+    if os.environ.get("TS2D_BIND", "1") == "0" or n_local <= 1 or not hasattr(os, "sched_setaffinity"):
+        return []
+    try:
+        allowed = sorted(os.sched_getaffinity(0))
+        cpus = [c for c in gpu_numa_cpus(pci_bus_id, sysfs) if c in allowed] if pci_bus_id else []
+        if not cpus:
+            per = len(allowed) // n_local
+            if per < 1:
+                return []
+            cpus = allowed[local_rank * per:(local_rank + 1) * per]
+        os.sched_setaffinity(0, cpus)
+        return cpus
+    except OSError:
+        return []
+
+
 def _dist():
     import torch.distributed as dist
     return dist if dist.is_available() and dist.is_initialized() else None
