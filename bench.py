@@ -50,7 +50,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--studies-per-step", type=int, default=4, help="studies each rank processes per step")
-    ap.add_argument("--precision", default=os.environ.get("TS2D_BENCH_PRECISION", "bf16"), choices=["bf16", "fp16"])
+    ap.add_argument("--precision", default=os.environ.get("TS2D_BENCH_PRECISION", "fp16"), choices=["bf16", "fp16"])
     ap.add_argument("--mirror", type=int, default=1, help="1: mirror TTA on (reference default), 0: off")
     ap.add_argument("--small", action="store_true", help="tiny shapes (debugging only; the JSON line says so)")
     ap.add_argument("--skip-cpu", action="store_true", help="omit the cpu_baseline leg")

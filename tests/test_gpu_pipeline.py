@@ -26,6 +26,27 @@ def _oracle_models(root, groups):
     return {f"ts2d-v2-ep4000b2_{g}": opipe.OracleModel(opipe.find_training_dir(os.path.join(root, f"ts2d-v2-ep4000b2_{g}", "r001"))) for g in groups}
 
 
+def test_bf16_masks_are_close_but_below_the_gate(zoo):
+    """bf16 storage (8 mantissa bits) on random-init weights: logits sit near the threshold, so ~0.5 % of the pixels flip against the
+    fp32 oracle.  That misses the 99.9 % gate, which is why fp16 - the reference's own autocast type on CUDA - is the default; bf16 stays
+    selectable (`b200.precision`) and must remain within 2 % (labels compared by name)."""
+    from totalsegmentator2d_b200.core.util.meta import get_annotation_labels
+    from totalsegmentator2d_b200.image import Image
+    from totalsegmentator2d_b200.tool import TS2D
+    root, groups = zoo
+    vol = synthetic_ct((150, 30, 100), seed=20260000)
+    d = np.diag([-1.0, -1.0, 1.0])
+    img = Image(vol, (1.5, 1.5, 1.5), (1.0, 2.0, 3.0), d.reshape(-1))
+    with TS2D(key="ts2d", models_root=root, param={"b200.precision": "bf16"}) as ts:
+        seg = ts.predict(img).get_segmentation()
+        merged = np.asarray(seg.array).reshape(150, 100, -1)
+        info = get_annotation_labels(seg, fetch=False)
+    ref = opipe.predict_study(vol, (1.5, 1.5, 1.5), d, _oracle_models(root, groups), mode="ideal")
+    agree = np.mean([np.mean(merged[..., info[n]["value"] - 1] == ref["segmentation"][..., i]) for i, n in enumerate(ref["names"])])
+    print(f"bf16: merged mask agreement {agree:.5f}")
+    assert agree >= 0.98
+
+
 @pytest.mark.parametrize("precision", ["fp32", "fp16"])
 def test_predict_3d_study_matches_oracle(zoo, precision):
     from totalsegmentator2d_b200.core.util.meta import get_annotation_labels

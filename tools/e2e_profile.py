@@ -21,7 +21,7 @@ def main():
     from totalsegmentator2d_b200.tool import TS2D
     tmp = tempfile.TemporaryDirectory()
     bench.write_zoo(tmp.name, False, True)
-    ts = TS2D(key="ts2d", models_root=tmp.name, param={"b200.precision": "bf16"})
+    ts = TS2D(key="ts2d", models_root=tmp.name, param={"b200.precision": os.environ.get("TS2D_PRECISION", "fp16")})
     vol = torch.from_numpy(bench.synthetic_volume(20260000)).pin_memory()
     img = Image(vol.numpy(), bench.SPACING, (0.0, 0.0, 0.0), np.eye(3).reshape(-1))
     for _ in range(3):

@@ -15,7 +15,7 @@ def main():
     from totalsegmentator2d_b200.tool import TS2D
     tmp = tempfile.TemporaryDirectory()
     bench.write_zoo(tmp.name, False, True)
-    ts = TS2D(key="ts2d", models_root=tmp.name, param={"b200.precision": "bf16"})
+    ts = TS2D(key="ts2d", models_root=tmp.name, param={"b200.precision": os.environ.get("TS2D_PRECISION", "fp16")})
     n_heads = ts.head_offsets()[-1]
     vol = torch.from_numpy(bench.synthetic_volume(20260000)).cuda()
     H, W = bench.VOL_SHAPE[0], bench.VOL_SHAPE[2]

@@ -35,7 +35,7 @@ def main():
     shape = (96, 64, 160) if small else bench.VOL_SHAPE
     tmp = tempfile.TemporaryDirectory()
     bench.write_zoo(tmp.name, small, True)
-    ts = TS2D(key="ts2d", models_root=tmp.name, param={"b200.precision": "bf16"})
+    ts = TS2D(key="ts2d", models_root=tmp.name, param={"b200.precision": os.environ.get("TS2D_PRECISION", "fp16")})
     home = 0
     vol = torch.from_numpy(bench.synthetic_volume(20260000, shape)).cuda() if rank == home else None
 

@@ -16,7 +16,7 @@ def main():
     tot = collections.OrderedDict()
     for r in rows:
         name = re.sub(r"\(.*", "", r[kn].replace("void ", "").replace("ts2d::", ""))
-        name = re.sub(r"<.*", "", name) if not name.startswith(("conv_", "project", "blend")) else re.sub(r"__nv_bfloat16", "bf16", name)
+        name = re.sub(r"<.*", "", name) if not name.startswith(("conv_", "project", "blend")) else re.sub(r"__half", "fp16", re.sub(r"__nv_bfloat16", "bf16", name))
         ns = float(r[mv].replace(",", "")) * {"ns": 1.0, "us": 1e3, "ms": 1e6}.get(r[mu], 1.0)
         n, t = tot.get(name, (0, 0.0))
         tot[name] = (n + 1, t + ns)

@@ -20,7 +20,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--batch", type=int, default=12)
     ap.add_argument("--heads", type=int, default=26)
-    ap.add_argument("--precision", default="bf16")
+    ap.add_argument("--precision", default="fp16")
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--patch", type=int, default=512)
     ap.add_argument("--out", default=None)

@@ -20,7 +20,7 @@ def main():
     ap.add_argument("--batch", type=int, default=12)
     ap.add_argument("--heads", type=int, default=26)
     ap.add_argument("--forwards", type=int, default=2)
-    ap.add_argument("--precision", default="bf16")
+    ap.add_argument("--precision", default="fp16")
     a = ap.parse_args()
     from totalsegmentator2d_b200 import _lib as L
     from totalsegmentator2d_b200 import synth

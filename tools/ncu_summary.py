@@ -45,6 +45,11 @@ def main():
     idx = {}
     for k, name in COLS.items():
         idx[k] = hdr.index(name) if name in hdr else -1
+    if idx["tensor_pct"] < 0 or all(r[idx["tensor_pct"]] in ("", "n/a", "0") for r in data):
+        # fp16 operands are counted by their own tensor-pipe metric
+        alt = COLS["tensor_pct"].replace("src_bf16", "src_fp16")
+        if alt in hdr:
+            idx["tensor_pct"] = hdr.index(alt)
     kn = hdr.index("Kernel Name")
 
     def val(r, k):

@@ -29,7 +29,7 @@ def main():
     tmp = tempfile.TemporaryDirectory()
     bench.write_zoo(tmp.name, False, True)
     os.environ["TS2D_MODEL_STREAMS"] = "1"
-    ts = TS2D(key="ts2d", models_root=tmp.name, param={"b200.precision": "bf16"})
+    ts = TS2D(key="ts2d", models_root=tmp.name, param={"b200.precision": os.environ.get("TS2D_PRECISION", "fp16")})
     vol = torch.from_numpy(bench.synthetic_volume(20260000)).cuda()
     for _ in range(3):
         ts.predict_volume_device(vol, bench.SPACING)

@@ -63,7 +63,7 @@ class NNUModel:
         self.augment = _get(param, "nnu.predict.augment", True, bool)
         self.stepsize = _get(param, "nnu.predict.stepsize", None, float)
         self.verbose = _get(param, "nnu.verbose", False, bool)
-        self.precision = _get(param, "b200.precision", "bf16", str)
+        self.precision = _get(param, "b200.precision", "fp16", str)
         self.use_tensor_cores = _get(param, "b200.tensor_cores", True, bool)
         self._colors = param.get("nnu.result.colors", "ts2d")
         self._configure()

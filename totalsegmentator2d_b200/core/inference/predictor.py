@@ -76,7 +76,7 @@ class _LabelManager:
 class B200nnUNetPredictor:
     def __init__(self, tile_step_size: float = 0.5, use_gaussian: bool = True, use_mirroring: bool = True,
                  perform_everything_on_device: bool = True, device=None, verbose: bool = False,
-                 verbose_preprocessing: bool = False, allow_tqdm: bool = False, precision: str = "bf16",
+                 verbose_preprocessing: bool = False, allow_tqdm: bool = False, precision: str = "fp16",
                  use_tensor_cores: bool = True, max_batch: int = 12):
         self.tile_step_size = tile_step_size
         self.use_gaussian = use_gaussian
