@@ -154,3 +154,18 @@ def test_combine_order_is_present_first():
     b[1, 1, 0] = 1
     merged, names = pipeline.combine_segmentations([a, b], [["x", "y", "z"], ["p", "q"]])
     assert names == ["z", "x", "y", "p", "q"] and merged.shape == (4, 4, 5) and merged[0, 0, 0] == 1
+
+
+def test_default_compute_type_is_the_references_autocast_type():
+    """fp16 (what nnU-Net's autocast computes in on CUDA) is the default storage type of the engine, the bench and the tools: it is the
+    16-bit type that meets the 99.9 % mask gate against the fp32 oracle (bf16: 0.9939 on random-init weights, tests/test_gpu_pipeline.py)"""
+    import inspect
+    import importlib.util
+    import os
+    from totalsegmentator2d_b200.core.inference.predictor import B200nnUNetPredictor
+    assert inspect.signature(B200nnUNetPredictor.__init__).parameters["precision"].default == "fp16"
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = open(os.path.join(root, "bench.py")).read()
+    assert 'os.environ.get("TS2D_BENCH_PRECISION", "fp16")' in src
+    src = open(os.path.join(root, "totalsegmentator2d_b200", "core", "inference", "nnu.py")).read()
+    assert '"b200.precision", "fp16"' in src
