@@ -169,3 +169,37 @@ def test_default_compute_type_is_the_references_autocast_type():
     assert 'os.environ.get("TS2D_BENCH_PRECISION", "fp16")' in src
     src = open(os.path.join(root, "totalsegmentator2d_b200", "core", "inference", "nnu.py")).read()
     assert '"b200.precision", "fp16"' in src
+
+
+def test_c_abi_library_exports_every_declared_symbol():
+    """the drop-in boundary: libts2d_b200.so loads without a GPU and exports every entry point include/ts2d_b200.h declares
+    (no compute call here); the product loader refuses to run without it (no CPU fallback)"""
+    import re
+    from totalsegmentator2d_b200 import _lib
+    hdr = open(os.path.join(ROOT, "include", "ts2d_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    hdr = re.sub(r"//[^\n]*", "", hdr)
+    names = sorted(set(re.findall(r"\b(ts2d_[a-z0-9_]+)\s*\(", hdr)))
+    assert len(names) >= 25 and "ts2d_project" in names and "ts2d_unet_forward" in names and "ts2d_unet_blend_head" in names
+    path = os.path.join(ROOT, "totalsegmentator2d_b200", "libts2d_b200.so")
+    assert os.path.exists(path), "build the extension first: python -c 'import __graft_entry__ as g; g.build()'"
+    lib = ctypes.CDLL(path)
+    missing = [n for n in names if not hasattr(lib, n)]
+    assert not missing, missing
+    lib.ts2d_abi_version.restype = ctypes.c_int
+    assert lib.ts2d_abi_version() == 1
+    lib.ts2d_last_error.restype = ctypes.c_char_p
+    assert isinstance(lib.ts2d_last_error(), (bytes, type(None)))
+    # the product path fails loudly when the library is absent, and without a GPU (this container has none)
+    import pytest
+    import torch
+    saved_lib, saved_path = _lib._lib, _lib.LIB_PATH
+    try:
+        _lib._lib, _lib.LIB_PATH = None, os.path.join(ROOT, "does_not_exist.so")
+        with pytest.raises(_lib.TS2DError, match="no CPU fallback"):
+            _lib.load()
+    finally:
+        _lib._lib, _lib.LIB_PATH = saved_lib, saved_path
+    if not torch.cuda.is_available():
+        with pytest.raises(_lib.TS2DError, match="no CUDA device"):
+            _lib.load(check_device=True)
