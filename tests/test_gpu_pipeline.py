@@ -157,3 +157,37 @@ def test_merge_present_order_on_device():
         assert perm.cpu().tolist() == want
         assert torch.equal(out.cpu(), src.cpu()[:, want])
         assert torch.equal(ops.permute_channels(src, want).cpu(), src.cpu()[:, want])
+
+
+def test_full_size_study_flip_equivariance_and_determinism():
+    """BASELINE size (512 x 512 x 1000 int16, five CS-512 group models, 3 tiles x 4 mirror passes each), size-independent properties of the
+    whole device path: (1) the same study twice gives the same bytes (split-K slices and statistics are reduced in a fixed order, atomics only
+    in fp64 sums that feed a rounding); (2) the sliding-window layout, the Gaussian and full mirror TTA are symmetric, so flipping the volume
+    along z flips the 117-channel mask up to the fp16 rounding of differently ordered sums (random-init logits sit near the threshold: 99.90 %
+    of the mask bytes measured, gate 99.8 %); (3) projections of the
+    flipped volume are the flipped projections, bit for bit."""
+    import tempfile
+    import bench
+    from totalsegmentator2d_b200.tool import TS2D
+    tmp = tempfile.TemporaryDirectory()
+    bench.write_zoo(tmp.name, False, True)
+    with TS2D(key="ts2d", models_root=tmp.name) as ts:
+        vol = torch.from_numpy(bench.synthetic_volume(20260007)).cuda()
+        ra = ts.predict_volume_device(vol, bench.SPACING, None)
+        a, pa = ra["mask"].clone(), {k: v.clone() for k, v in ra["projections"].items()} if isinstance(ra["projections"], dict) else ra["projections"].clone()
+        again = ts.predict_volume_device(vol, bench.SPACING, None)["mask"]
+        same = float((a == again).float().mean())
+        assert same >= 0.99999, same
+        volf = torch.flip(vol, dims=[0]).contiguous()
+        rb = ts.predict_volume_device(volf, bench.SPACING, None)
+        b = torch.flip(rb["mask"], dims=[0])
+        assert a.shape == (1000, 512, 117)
+        agree = float((a == b).float().mean())
+        print(f"full-size flip equivariance: {agree:.6f}, repeatability {same:.6f}, foreground fraction {float(a.float().mean()):.4f}")
+        assert agree >= 0.998, agree
+        if isinstance(pa, dict):
+            for k in pa:
+                assert torch.equal(pa[k], torch.flip(rb["projections"][k], dims=[-2]))
+        else:
+            assert torch.equal(pa, torch.flip(rb["projections"], dims=[-2]))
+        torch.cuda.synchronize()
