@@ -142,10 +142,16 @@ project_strided_i16_kernel(ProjParams p, int xt /*threads along x*/, int yt /*gr
 }
 
 // ---------------- generic strided path: one column per thread -------------------------------------------------
+// extrema are tracked in the voxel type when that is exact and cheaper (float: FMNMX instead of three fp64 operations per voxel);
+// the sum stays in sum_t (double / 64-bit integer: mean = exact-as-ITK double sum / N)
+template <typename T> struct Ext { using type = double; };
+template <> struct Ext<float> { using type = float; };
 template <typename T>
 __global__ void __launch_bounds__(256)
 project_strided_generic_kernel(ProjParams p, int yt, long long n_items, int xchunks) {
     using sum_t = typename Acc<T>::sum_t;
+    using ext_t = typename Ext<T>::type;
+    constexpr int kU = 8;                       // independent loads in flight per thread
     __shared__ double s_sum[256];
     __shared__ double s_max[256];
     __shared__ double s_min[256];
@@ -156,30 +162,30 @@ project_strided_generic_kernel(ProjParams p, int yt, long long n_items, int xchu
         const long long o = item / xchunks;
         const long long x = (item % xchunks) * xt + tx;
         sum_t s = 0;
-        double mx = -1.7976931348623157e308, mn = 1.7976931348623157e308;
+        ext_t mx = (ext_t)-1.7976931348623157e308, mn = (ext_t)1.7976931348623157e308;     // float: -inf / +inf
         if (x < p.X && ty < yt) {
             const T *base = vol + o * p.ostride + x;
-            for (long long y = ty; y < p.R; y += (long long)yt * 4) {
-                T v[4];
+            for (long long y = ty; y < p.R; y += (long long)yt * kU) {
+                T v[kU];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
+                for (int j = 0; j < kU; ++j) {
                     const long long yy = y + (long long)j * yt;
                     v[j] = yy < p.R ? base[yy * p.rstride] : T(0);
                 }
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
+                for (int j = 0; j < kU; ++j) {
                     const long long yy = y + (long long)j * yt;
                     if (yy < p.R) {
                         s += (sum_t)v[j];
-                        mx = fmax(mx, (double)v[j]);
-                        mn = fmin(mn, (double)v[j]);
+                        mx = v[j] > mx ? (ext_t)v[j] : mx;
+                        mn = v[j] < mn ? (ext_t)v[j] : mn;
                     }
                 }
             }
         }
         s_sum[threadIdx.x] = (double)s;   // exact: |s| < 2^53 for every supported integer type and size
-        s_max[threadIdx.x] = mx;
-        s_min[threadIdx.x] = mn;
+        s_max[threadIdx.x] = (double)mx;
+        s_min[threadIdx.x] = (double)mn;
         __syncthreads();
         if (ty == 0 && x < p.X) {
             double ss = 0, a = -1.7976931348623157e308, b = 1.7976931348623157e308;
