@@ -460,6 +460,14 @@ def run_b200(args):
             conv_traffic = float(tj["conv_dram_bytes_per_forward"]) * len(preds)
     except Exception:
         conv_traffic = None
+    # same for the projection kernel (one launch = one study's volume): ncu --set full capture of tools/projection_sweep.py
+    proj_traffic = None
+    try:
+        pj = tj.get("project_strided_i16_kernel")
+        if pj and tuple(pj["volume"]) == tuple(shape):
+            proj_traffic = float(pj["dram_read_bytes"]) + float(pj["dram_write_bytes"])
+    except Exception:
+        proj_traffic = None
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
@@ -473,7 +481,7 @@ def run_b200(args):
                              "peak_source": peak_src + " (sustained)",
                              "conv_ms_per_study": conv_ms, "conv_flops_per_study": conv_flops},
                 "roofline_hbm": {"bound": "hbm", "kernel": "project_strided_i16_kernel", "achieved": proj_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                                 "frac": proj_gbs / peaks["hbm_gbs"], "traffic": None, "peak_source": peak_src, "ms": proj_ms, "bytes": proj_bytes},
+                                 "frac": proj_gbs / peaks["hbm_gbs"], "traffic": proj_traffic, "peak_source": peak_src, "ms": proj_ms, "bytes": proj_bytes},
                 "cpu_baseline": cpu}
         print(json.dumps(line))
     ts.close()

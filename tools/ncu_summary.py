@@ -76,8 +76,14 @@ def main():
             int(val(r, "regs"))))
     lines.append("# total: %.1f us under ncu, DRAM read+write %.1f MB per forward of %d tiles" % (tot_us, tot_b / 1e6, a.batch))
     open(a.out_txt, "w").write("\n".join(lines) + "\n")
-    json.dump({"source": os.path.basename(a.raw_csv), "batch": a.batch, "conv_dram_bytes_per_forward": tot_b, "launches": per},
-              open(a.json, "w"), indent=1)
+    keep = {}
+    try:
+        keep = {k: v for k, v in json.load(open(a.json)).items() if k not in ("source", "batch", "conv_dram_bytes_per_forward", "launches")}
+    except Exception:
+        keep = {}
+    out = {"source": os.path.basename(a.raw_csv), "batch": a.batch, "conv_dram_bytes_per_forward": tot_b, "launches": per}
+    out.update(keep)        # other kernels' captures (e.g. project_strided_i16_kernel) live in the same file
+    json.dump(out, open(a.json, "w"), indent=1)
     print("\n".join(lines))
 
 
