@@ -101,11 +101,14 @@ def project_study(vol_zyx: np.ndarray, direction, channel_names: Sequence[str]) 
 
 def combine_segmentations(segs: List[np.ndarray], names: List[List[str]]):
     """reference image.py:490-510: per model, labels present in the mask first
-    (ascending), then the absent ones in metadata order (meta.py:280-286)."""
+    (ascending, meta.py:15-49), then the absent ones in metadata order (meta.py:254-286).
+    Metadata order = sitk ``GetMetaDataKeys()`` = keys of a std::map, i.e. the segment ids
+    sorted by the STRING "Segment{id}_" (0, 10, 11, ..., 19, 1, 20, ...; '_' sorts after digits)."""
     chans, out_names = [], []
     for seg, nm in zip(segs, names):
         present = [i for i in range(seg.shape[-1]) if seg[..., i].any()]
-        absent = [i for i in range(seg.shape[-1]) if i not in present]
+        lex = sorted(range(seg.shape[-1]), key=lambda i: f"Segment{i}_".encode())
+        absent = [i for i in lex if i not in present]
         for i in present + absent:
             chans.append((seg[..., i] > 0).astype(np.uint8))
             out_names.append(nm[i])

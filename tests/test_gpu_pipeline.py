@@ -153,7 +153,8 @@ def test_merge_present_order_on_device():
         want = []
         for m in range(len(offs) - 1):
             cs = list(range(offs[m], offs[m + 1]))
-            want += [c for c in cs if p[c]] + [c for c in cs if not p[c]]
+            lex = sorted(cs, key=lambda c: f"Segment{c - offs[m]}_")       # std::map key order of sitk GetMetaDataKeys()
+            want += [c for c in cs if p[c]] + [c for c in lex if not p[c]]
         assert perm.cpu().tolist() == want
         assert torch.equal(out.cpu(), src.cpu()[:, want])
         assert torch.equal(ops.permute_channels(src, want).cpu(), src.cpu()[:, want])

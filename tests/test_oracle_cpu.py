@@ -156,6 +156,29 @@ def test_combine_order_is_present_first():
     assert names == ["z", "x", "y", "p", "q"] and merged.shape == (4, 4, 5) and merged[0, 0, 0] == 1
 
 
+def test_combine_order_absent_labels_follow_std_map_key_order():
+    """reference meta.py:254-286 walks sitk GetMetaDataKeys() (a std::map): absent labels come out in the lexicographic order of
+    "Segment{id}_" (0, 10, 11, 1, 2, ...), not ascending.  12 labels, channels 2 and 11 present -> 2, 11, then 0, 10, 1, 3, 4, ...
+    Pinned for the oracle and for the host mirror of combine_segmentations (same Image metadata semantics)."""
+    from totalsegmentator2d_b200.core.util.image import combine_segmentations
+    from totalsegmentator2d_b200.core.util.meta import get_annotation_labels, set_annotation_meta
+    from totalsegmentator2d_b200.image import Image
+    a = np.zeros((4, 4, 12), np.uint8)
+    a[0, 0, 2] = 1
+    a[1, 1, 11] = 1
+    nm = [f"n{i}" for i in range(12)]
+    want = ["n2", "n11", "n0", "n10", "n1", "n3", "n4", "n5", "n6", "n7", "n8", "n9"]
+    merged, names = pipeline.combine_segmentations([a], [nm])
+    assert names == want and merged[0, 0, 0] == 1 and merged[1, 1, 1] == 1
+    seg = Image(a, is_vector=True)
+    set_annotation_meta(seg, names={i + 1: n for i, n in enumerate(nm)}, colors={})
+    assert seg.GetMetaDataKeys()[0] == "Segment0_ID" and seg.GetMetaDataKeys().index("Segment10_ID") < seg.GetMetaDataKeys().index("Segment1_ID")
+    out = combine_segmentations([seg])
+    got = [v["name"] for v in sorted(get_annotation_labels(out, fetch=False).values(), key=lambda v: v["value"])]
+    assert got == want
+    assert np.array_equal(np.asarray(out.array), merged)
+
+
 def test_default_compute_type_is_the_references_autocast_type():
     """fp16 (what nnU-Net's autocast computes in on CUDA) is the default storage type of the engine, the bench and the tools: it is the
     16-bit type that meets the 99.9 % mask gate against the fp32 oracle (bf16: 0.9939 on random-init weights, tests/test_gpu_pipeline.py)"""

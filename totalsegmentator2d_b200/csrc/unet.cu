@@ -14,6 +14,7 @@
 //   tmpA/B   normalised intermediates / decoder stage outputs
 #include <algorithm>
 #include <map>
+#include <string>
 #include <vector>
 
 #include "conv_tc.cuh"
@@ -1136,6 +1137,14 @@ extern "C" int ts2d_merge_present_order(const uint8_t *src_dev, uint8_t *dst_dev
     for (int m = 0; m <= n_models; ++m) {
         TS2D_REQUIRE(m == 0 || offsets_host[m] >= offsets_host[m - 1], "ts2d_merge_present_order: offsets must be ascending");
         mo.off[m] = offsets_host[m];
+    }
+    for (int m = 0; m < n_models; ++m) {
+        // segment ids of model m in the order of the keys "Segment{id}_" in a std::map (what sitk GetMetaDataKeys() returns)
+        const int lo = offsets_host[m], n = offsets_host[m + 1] - lo;
+        std::vector<std::pair<std::string, int>> keys;
+        for (int i = 0; i < n; ++i) keys.push_back({"Segment" + std::to_string(i) + "_", i});
+        std::sort(keys.begin(), keys.end());
+        for (int i = 0; i < n; ++i) mo.lex[lo + i] = lo + keys[i].second;
     }
     cudaStream_t st = (cudaStream_t)stream;
     present_order_kernel<<<1, 32, 0, st>>>(present_dev, mo, perm_dev);

@@ -603,14 +603,17 @@ __global__ void __launch_bounds__(128) permute_channels_kernel(const uint8_t *sr
 }
 
 // perm for the reference's merged channel order: per model, labels present in the image first (ascending), then the absent
-// ones (reference ts2d/core/util/meta.py:280-286).  One thread per model; offsets[m]..offsets[m+1] is model m's channel window.
-struct ModelOffsets { int n_models; int off[33]; };
+// ones in the order get_annotation_meta meets them (reference ts2d/core/util/meta.py:254-286): that loop walks
+// sitk GetMetaDataKeys(), i.e. a std::map, so segment ids come out in LEXICOGRAPHIC order of "Segment{id}_" (0, 10, 11, ..., 19,
+// 1, 20, ...).  lex[] holds, per model window, the window's channels in that order (host-computed, see ts2d_merge_present_order).
+// One thread per model; offsets[m]..offsets[m+1] is model m's channel window.
+struct ModelOffsets { int n_models; int off[33]; int lex[256]; };
 __global__ void present_order_kernel(const uint8_t *present, const __grid_constant__ ModelOffsets mo, int *perm) {
     const int m = threadIdx.x;
     if (m >= mo.n_models) return;
     int k = mo.off[m];
     for (int c = mo.off[m]; c < mo.off[m + 1]; ++c) if (present[c]) perm[k++] = c;
-    for (int c = mo.off[m]; c < mo.off[m + 1]; ++c) if (!present[c]) perm[k++] = c;
+    for (int j = mo.off[m]; j < mo.off[m + 1]; ++j) { const int c = mo.lex[j]; if (!present[c]) perm[k++] = c; }
 }
 
 // NHWC (pixel stride ps) -> float32 NCHW (layer-wise parity tests)

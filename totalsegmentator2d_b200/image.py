@@ -93,7 +93,10 @@ class Image:
 
     # --- metadata dictionary -------------------------------------------------
     def GetMetaDataKeys(self):
-        return tuple(self._meta.keys())
+        # itk::MetaDataDictionary is a std::map<std::string, ...>: keys come out in byte-wise lexicographic order
+        # ("Segment0_", "Segment10_", ..., "Segment19_", "Segment1_", "Segment20_", ...).  combine_segmentations relies on
+        # that order for the labels that are absent from the image (reference ts2d/core/util/meta.py:254-286).
+        return tuple(sorted(self._meta.keys(), key=lambda k: k.encode("utf-8")))
 
     def GetMetaData(self, key: str) -> str:
         return self._meta[key]
