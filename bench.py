@@ -87,6 +87,23 @@ def synthetic_volume(seed: int, shape=VOL_SHAPE) -> np.ndarray:
     return vol
 
 
+# 16 of the 64 studies are stored with permuted / flipped axes (reorient_image folded into the projection
+# addressing): study i with i % 8 == 3 has x and y swapped (the coronal reduction runs along the CONTIGUOUS axis), i % 8 == 7 has
+# y and z swapped (reduction along the slowest axis); both with flips.  The RAI view of every study is [z=1000][y=512][x=512].
+_D_XY = np.array([[0.0, -1.0, 0.0], [1.0, 0.0, 0.0], [0.0, 0.0, -1.0]])
+_D_ZY = np.array([[1.0, 0.0, 0.0], [0.0, 0.0, -1.0], [0.0, 1.0, 0.0]])
+
+
+def study_orientation(i: int, shape):
+    """(direction matrix, stored [n0][n1][n2] shape) of study i; RAI-reoriented it is ``shape``"""
+    nz, ny, nx = shape
+    if i % 8 == 3:
+        return _D_XY, (nz, nx, ny)
+    if i % 8 == 7:
+        return _D_ZY, (ny, nz, nx)
+    return np.eye(3), (nz, ny, nx)
+
+
 def write_zoo(root: str, small: bool, mirror: bool, only=None):
     """returns (all five groups, patch); ``only`` restricts which model directories are written (seeds unchanged)"""
     from totalsegmentator2d_b200 import synth
@@ -152,10 +169,12 @@ class ClockSampler:
 # CPU leg: the oracle (restatement of the reference's SimpleITK + nnU-Net + torch-CPU path) on the host cores
 # ----------------------------------------------------------------------------------------------------------
 class CpuReference:
-    """Times the reference path per stage on a BOUNDED sample of the workload and scales to one study:
-    projection (C/OpenMP restatement of the two ITK filters, full volume) + preprocessing (full image) +
-    sliding-window U-Net of ONE tile (of T) with its mirror passes for ONE model (of 5) + export (full image,
-    one model).  study_seconds = t_proj + n_models * (t_pre + T * t_tile + t_export)."""
+    """The reference path on the host cores, WHOLE studies, wall to wall (no extrapolation): reorient -> max / mean projection ->
+    per group model: crop / normalise / resample -> every sliding-window tile x every mirror pass through the fp32 U-Net ->
+    Gaussian blend -> sigmoid / threshold / un-crop -> merge of the five masks into the 117-label mask
+    (oracle.pipeline.predict_study: stage order of reference ts2d/tool.py:85-179 and prediction_worker.py:177-242, with the
+    reference's own stage names).  The projection uses the C + OpenMP restatement (stand-in for ITK's multi-threaded filters),
+    the U-Net torch-CPU with every core."""
 
     def __init__(self, zoo_root: str, groups, mirror: bool):
         import ctypes
@@ -165,88 +184,75 @@ class CpuReference:
         self.groups = list(groups)
         torch.set_num_threads(os.cpu_count() or 1)
         self.cores = torch.get_num_threads()
-        g = "ribs" if "ribs" in self.groups else self.groups[0]
-        self.model = opipe.OracleModel(opipe.find_training_dir(os.path.join(zoo_root, f"{MODEL_KEY}_{g}", "r001")))
+        self.models = {f"{MODEL_KEY}_{g}": opipe.OracleModel(opipe.find_training_dir(os.path.join(zoo_root, f"{MODEL_KEY}_{g}", "r001")))
+                       for g in self.groups}
         so = os.path.join(ROOT, "oracle", "liboracle_projection.so")
         self.clib = ctypes.CDLL(so) if os.path.exists(so) else None
 
-    def project(self, vol: np.ndarray) -> np.ndarray:
+    def _project(self, vol: np.ndarray, name: str) -> np.ndarray:
         import ctypes
-        nz, ny, nx = vol.shape
-        out = np.empty((2, nz, nx), dtype=np.float32)
-        if self.clib is not None and vol.dtype == np.int16:
-            for i, fn in enumerate((self.clib.oracle_project_mean_i16, self.clib.oracle_project_max_i16)):
-                fn.restype = None
-                fn(vol.ctypes.data_as(ctypes.c_void_p), ctypes.c_int64(nz), ctypes.c_int64(ny), ctypes.c_int64(nx),
-                   out[i].ctypes.data_as(ctypes.c_void_p))
-            return out
         from oracle import geometry
-        return geometry.project_channels(vol, ["mean", "max"])
+        if self.clib is None or vol.dtype != np.int16 or name not in ("mean", "max"):
+            return geometry.project_channels(vol, [name])[0]
+        nz, ny, nx = vol.shape
+        out = np.empty((nz, nx), dtype=np.float32)
+        fn = self.clib.oracle_project_mean_i16 if name == "mean" else self.clib.oracle_project_max_i16
+        fn.restype = None
+        fn(vol.ctypes.data_as(ctypes.c_void_p), ctypes.c_int64(nz), ctypes.c_int64(ny), ctypes.c_int64(nx), out.ctypes.data_as(ctypes.c_void_p))
+        return out
 
-    def sample(self, vol: np.ndarray) -> dict:
-        from oracle import nnunet_inf, nnunet_pre
-        m = self.model
+    def study(self, vol: np.ndarray, direction=None) -> dict:
+        """one whole study; returns wall seconds and the per-stage split"""
+        st = {}
         t0 = time.perf_counter()
-        img = self.project(vol)
-        t1 = time.perf_counter()
-        with torch.no_grad():
-            sp = nnunet_pre.sitkio_spacing_2d((SPACING[0], SPACING[2]))
-            pre, props = nnunet_pre.run_case_npy(img[:, None], sp, m.spacing, m.schemes, m.intensity_props, m.use_mask_for_norm)
-            t2 = time.perf_counter()
-            x = torch.from_numpy(pre)
-            padded, _, _ = nnunet_inf.pad_to_patch(x, m.patch_size)
-            steps = nnunet_inf.compute_steps_for_sliding_window(padded.shape[2:], m.patch_size, 0.5)
-            n_tiles = len(steps[0]) * len(steps[1])
-            tile = padded[:, 0, :m.patch_size[0], :m.patch_size[1]][None]
-            t3 = time.perf_counter()
-            pred = nnunet_inf.maybe_mirror_and_predict(m.net(m.state_dicts[0]), tile, m.mirror_axes if self.mirror else None)
-            t4 = time.perf_counter()
-            logits = pred[0][:, None, :pre.shape[2], :pre.shape[3]]
-            if logits.shape[2:] != pre.shape[2:]:      # image taller than one tile: export a full-size logit map
-                logits = torch.nn.functional.pad(logits, (0, pre.shape[3] - logits.shape[3], 0, pre.shape[2] - logits.shape[2]))
-            seg = nnunet_inf.export_multilabel(logits.numpy(), props, "ideal")
-            t5 = time.perf_counter()
-        n_models = len(self.groups)
-        study = (t1 - t0) + n_models * ((t2 - t1) + n_tiles * (t4 - t3) + (t5 - t4))
-        return {"study_seconds": study, "projected": t1 - t0, "preprocessed": t2 - t1, "tile_predicted": t4 - t3, "exported": t5 - t4,
-                "n_tiles": n_tiles, "n_models": n_models, "mask_shape": list(seg.shape)}
+        res = self.opipe.predict_study(vol, SPACING, np.eye(3) if direction is None else direction, self.models, 0.5, self.mirror, "ideal", st,
+                                       project_fn=self._project)
+        wall = time.perf_counter() - t0
+        return {"study_seconds": wall, "stages": {k: float(v) for k, v in st.items()}, "mask_shape": list(res["segmentation"].shape)}
 
     def describe(self, shape) -> str:
-        return ("1 study {}x{}x{} int16: projection (full volume) + preprocess + 1 of T tiles x {} mirror passes of 1 of {} "
-                "group models + export, scaled to T tiles x {} models").format(shape[2], shape[1], shape[0], 4 if self.mirror else 1,
-                                                                               len(self.groups), len(self.groups))
+        return ("whole studies {}x{}x{} int16, wall to wall: projection + 5 group models x (preprocess + all tiles x {} mirror passes + "
+                "blend + export) + 117-label merge; nothing extrapolated").format(shape[2], shape[1], shape[0], 4 if self.mirror else 1)
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU implementation of the path.  The reference itself cannot run here
-    (SimpleITK / nnunetv2ml / weights are not installable offline), so this is the oracle port."""
+    """--impl reference: the reference's CPU implementation of the path.  The reference itself cannot run here (SimpleITK /
+    nnunetv2ml / weights are not installable offline), so this is the oracle port (kind "port").
+    One step = ONE whole study, timed wall to wall: a bounded sample of the GPU arm's step (S studies), so that
+    ``--steps 20 --warmup 5`` ends within a few minutes at ~7 s per study; config is the GPU arm's."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     shape = (96, 64, 160) if args.small else VOL_SHAPE
+    S = max(1, args.studies_per_step)
     with tempfile.TemporaryDirectory() as tmp:
-        groups, patch = write_zoo(tmp, args.small, bool(args.mirror), only=("ribs",))
+        groups, patch = write_zoo(tmp, args.small, bool(args.mirror))
         ref = CpuReference(tmp, groups, bool(args.mirror))
-        vol = synthetic_volume(20260000, shape)
+        vols = [synthetic_volume(20260000 + i, shape) for i in range(2)]
         times = []
+        t_all = time.perf_counter()
         for i in range(args.warmup + args.steps):
-            s = ref.sample(vol)
+            s = ref.study(vols[i % len(vols)])
             if i >= args.warmup:
                 times.append(s)
+        t_all = time.perf_counter() - t_all
     study = float(np.mean([t["study_seconds"] for t in times])) if times else float("nan")
     v = 1.0 / study
+    stages = {k: float(np.mean([t["stages"].get(k, 0.0) for t in times])) for k in ("projected", "preprocessed", "predicted", "exported", "merged")}
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1000.0 * study, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": config_dict(args, shape, patch, 1),
-            "cpu_baseline": {"value": v, "unit": UNIT, "cores": ref.cores, "kind": "port", "sample": ref.describe(shape),
-                             "stage_seconds": {k: float(np.mean([t[k] for t in times])) for k in ("projected", "preprocessed", "tile_predicted", "exported")}},
+            "config": config_dict(args, shape, patch, S),
+            "step_sample": "each step times 1 whole study (of the {} a GPU-arm step holds); value = 1 / mean study wall time".format(S),
+            "wall_s_all_steps": t_all,
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": ref.cores, "kind": "port", "sample": ref.describe(shape), "stage_seconds": stages},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line))
 
 
 def config_dict(args, shape, patch, studies_per_step):
     return {"workload": "ts2d-v2 5-model pipeline, synthetic CT {}x{}x{} int16 1.5mm, CS-{} plan, 117 labels".format(shape[2], shape[1], shape[0], patch[0]),
-            "studies_per_step_per_gpu": studies_per_step, "tile_step_size": 0.5, "mirror_tta": bool(args.mirror), "models": 5,
+            "studies_per_step_per_gpu": studies_per_step, "orientations": "study i: i%8==3 x/y swapped + flips, i%8==7 y/z swapped + flips, else RAI",
+            "tile_step_size": 0.5, "mirror_tta": bool(args.mirror), "models": 5,
             "parallelism": "studies sharded over GPUs, no collective", "l2": "inputs larger than L2 (524 MB per study)",
             "small": bool(args.small)}
 
@@ -312,11 +318,13 @@ def run_b200(args):
     n_heads = ts.head_offsets()[-1]
 
     # synthetic studies: S distinct volumes per rank, pinned on the host and resident in HBM
-    host_vols = []
+    host_vols, dirs = [], []
     from totalsegmentator2d_b200 import shard
     for i in shard.shard_indices(S * world, rank, world):      # study i -> rank i mod world
-        v = torch.from_numpy(synthetic_volume(20260000 + i, shape)).pin_memory()
+        d, shp = study_orientation(i, shape)
+        v = torch.from_numpy(synthetic_volume(20260000 + i, shp)).pin_memory()
         host_vols.append(v)
+        dirs.append(d)
     dev_vols = [v.cuda(non_blocking=True) for v in host_vols]
     H, W = shape[0], shape[2]
     masks = [torch.zeros((H, W, n_heads), dtype=torch.uint8, device="cuda") for _ in range(S)]
@@ -331,7 +339,7 @@ def run_b200(args):
         # one study = projection -> preprocess -> 5 group U-Nets -> blend / threshold -> merged 117-channel mask in the
         # reference's channel order (combine_segmentations), everything resident in HBM
         for i in range(S):
-            ts.predict_volume_device(dev_vols[i], SPACING, None, mask=masks[i], present=presents[i])
+            ts.predict_volume_device(dev_vols[i], SPACING, dirs[i], mask=masks[i], present=presents[i])
             _ops.merge_present_order(masks[i], presents[i], offs, out=merged[i])
 
     def launches_now():
@@ -382,6 +390,7 @@ def run_b200(args):
     else:
         os.environ["TS2D_MODEL_STREAMS"] = prev_streams
     conv_ms = sum(p.last_conv_ms() for p in preds)
+    unet_ms = sum(p.last_forward_ms() for p in preds)       # convs + InstanceNorm-apply + split-K finish launches
     for p in preds:
         p.set_profiling(False)
     M = 4 if args.mirror else 1
@@ -397,8 +406,9 @@ def run_b200(args):
     out = torch.empty((2, H, W), dtype=torch.float32, device="cuda")
     reps = 10
     pms = []
+    ident = [k for k in range(S) if np.array_equal(dirs[k], np.eye(3))]      # the RAI-stored studies (reduce over n1)
     for r in range(reps):
-        v = dev_vols[r % S]
+        v = dev_vols[ident[r % len(ident)]]
         pe0.record()
         ops.project(v, ["mean", "max"], reduce_dim=1, h_dim=0, out=out)
         pe1.record()
@@ -411,7 +421,7 @@ def run_b200(args):
     # ---- e2e: public API, host buffers ------------------------------------------------------------------------
     e2e = None
     if not args.skip_e2e:
-        imgs = [Image(host_vols[i].numpy(), SPACING, (0.0, 0.0, 0.0), np.eye(3).reshape(-1)) for i in range(S)]
+        imgs = [Image(host_vols[i].numpy(), SPACING, (0.0, 0.0, 0.0), dirs[i].reshape(-1)) for i in range(S)]
 
         def run_e2e(n_steps):
             """n_steps x S studies through the public batch API: every study's volume is copied from pinned host memory
@@ -446,9 +456,9 @@ def run_b200(args):
     cpu = None
     if rank == 0 and world == 1 and not args.skip_cpu:
         ref = CpuReference(tmp.name, groups, bool(args.mirror))
-        s = ref.sample(host_vols[0].numpy())
-        cpu = {"value": 1.0 / s["study_seconds"], "unit": UNIT, "cores": ref.cores, "kind": "port", "sample": ref.describe(shape),
-               "stage_seconds": {k: s[k] for k in ("projected", "preprocessed", "tile_predicted", "exported")}}
+        s = ref.study(host_vols[0].numpy())           # ONE whole study, wall to wall (~7 s on 16 cores)
+        cpu = {"value": 1.0 / s["study_seconds"], "unit": UNIT, "cores": ref.cores, "kind": "port",
+               "sample": "1 of the step's studies: " + ref.describe(shape), "stage_seconds": s["stages"]}
 
     # DRAM bytes of the conv launches measured by ncu --set full (tools/ncu_summary.py -> profiles/ncu_traffic.json),
     # scaled from the captured forward (batch of tiles x mirrors of ONE model) to one study (all group models)
@@ -479,7 +489,10 @@ def run_b200(args):
                              "frac": conv_tflops / peaks["bf16_tflops_sustained"], "traffic": conv_traffic,
                              "traffic_note": "DRAM read+write bytes of the conv launches of one study (ncu --set full, profiles/ncu_traffic.json); the step is one study's launches, so achieved/traffic are per study",
                              "peak_source": peak_src + " (sustained)",
-                             "conv_ms_per_study": conv_ms, "conv_flops_per_study": conv_flops},
+                             "conv_ms_per_study": conv_ms, "conv_flops_per_study": conv_flops,
+                             "frac_unet": (conv_flops / (unet_ms * 1e-3) / 1e12) / peaks["bf16_tflops_sustained"] if unet_ms > 0 else None,
+                             "unet_ms_per_study": unet_ms,
+                             "frac_unet_note": "conv FLOPs / ALL U-Net launches of one study (convs + InstanceNorm-apply + split-K finish)"},
                 "roofline_hbm": {"bound": "hbm", "kernel": "project_strided_i16_kernel", "achieved": proj_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                                  "frac": proj_gbs / peaks["hbm_gbs"], "traffic": proj_traffic, "peak_source": peak_src, "ms": proj_ms, "bytes": proj_bytes},
                 "cpu_baseline": cpu}

@@ -175,6 +175,9 @@ double ts2d_unet_flops(const ts2d_unet *u, int batch);
 /* device time (ms) the conv kernels of the last forward took; needs ts2d_unet_set_profiling(u, 1) */
 int ts2d_unet_set_profiling(ts2d_unet *u, int enable);
 double ts2d_unet_last_conv_ms(ts2d_unet *u);
+/* same, summed over EVERY launch of the last forward (convs, transposed convs, InstanceNorm-apply and split-K finish passes):
+ * the denominator of the honest U-Net roofline fraction (bench.py roofline.frac_unet) */
+double ts2d_unet_last_forward_ms(ts2d_unet *u);
 /* per-launch record of the last profiled forward: kind 0 = conv, 1 = transposed conv, 2 = InstanceNorm-apply;
  * flops / bytes are the ALGORITHMIC figures of that launch (MAC = 2; bytes = activations read once + written once) */
 int ts2d_unet_profile_count(const ts2d_unet *u);

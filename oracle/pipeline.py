@@ -116,8 +116,10 @@ def combine_segmentations(segs: List[np.ndarray], names: List[List[str]]):
 
 
 def predict_study(vol_zyx: np.ndarray, spacing_xyz, direction, models: Dict[str, OracleModel], tile_step_size=0.5,
-                  use_mirroring=True, mode="ideal", stage_times: Optional[dict] = None):
-    """3-D study -> {'projections': (C,H,W), 'models': {id: mask}, 'segmentation': merged, 'names': [...]}"""
+                  use_mirroring=True, mode="ideal", stage_times: Optional[dict] = None, project_fn=None):
+    """3-D study -> {'projections': (C,H,W), 'models': {id: mask}, 'segmentation': merged, 'names': [...]}
+    ``project_fn(vol_rai, name) -> float32 (H, W)`` replaces the numpy projection (bench.py passes the C + OpenMP
+    restatement, which stands in for ITK's multi-threaded filters when the CPU path is TIMED; results are identical)."""
     t0 = time.time()
     ids = sorted(models.keys())
     first = models[ids[0]]
@@ -133,7 +135,7 @@ def predict_study(vol_zyx: np.ndarray, spacing_xyz, direction, models: Dict[str,
         ta = time.time()
         for name in m.channel_names:
             if name not in cache:
-                cache[name] = geometry.project_channels(rai, [name])[0]
+                cache[name] = project_fn(rai, name) if project_fn is not None else geometry.project_channels(rai, [name])[0]
         img = np.stack([cache[n] for n in m.channel_names], axis=0)
         tb = time.time()
         t_proj += tb - ta

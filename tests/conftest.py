@@ -38,3 +38,17 @@ def synthetic_ct(shape_zyx, seed, dtype=np.int16):
 @pytest.fixture(scope="session")
 def golden_dir():
     return GOLDEN
+
+
+@pytest.fixture(scope="session")
+def cs512_zoo(tmp_path_factory):
+    """the BASELINE zoo (five CS-512 group models, heads 18/23/24/26/26, seeds 1000+g as bench.py) written once per session"""
+    import bench
+    root = str(tmp_path_factory.mktemp("cs512_zoo"))
+    groups, patch = bench.write_zoo(root, False, True)
+    return root, groups
+
+
+def oracle_models(root, model_key, groups):
+    from oracle import pipeline as opipe
+    return {f"{model_key}_{g}": opipe.OracleModel(opipe.find_training_dir(os.path.join(root, f"{model_key}_{g}", "r001"))) for g in groups}

@@ -1,0 +1,154 @@
+"""GPU parity for the BASELINE.json / SURVEY 8d configurations other than the headline one, all at the CS-512 plan and through the
+public API, each against the CPU oracle per label name with the north_star gate (>= 99.9 % pixel agreement):
+
+  config 3   tsxr-v2 on assets/sample_chexpert.nrrd (uint8 320 x 320, spacing 1.25, ONE channel, no projection), plan spacing
+             1.25 (no resampling) and 1.0 (320^2 -> 400^2: cubic resampling in, order-1 logit resampling out)
+             [reference test/test_020_predict_default.py:41-59, ts2d/data/config.json:4]
+  config 4B  a 0.75 mm study: projection -> crop -> z-score -> resample to 1.5 mm (500 x 256) -> U-Nets -> logits resampled
+             back -> threshold -> 117-label mask
+  config 4   a study whose direction matrix permutes and flips the axes (reorient_image folded into the projection addressing)
+  operator   the reference worker's three calls replayed literally (prediction_worker.py:194-221): preprocessor_class(...).run_case
+             -> predict_logits_from_preprocessed_data -> export_prediction_from_logits -> the written .nrrd
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import geometry
+from oracle import pipeline as opipe
+from tests.conftest import GOLDEN, oracle_models
+
+pytestmark = pytest.mark.gpu
+MASK_GATE = 0.999
+
+
+def _per_label_agreement(seg_img, shape_hw, ref_seg, ref_names):
+    from totalsegmentator2d_b200.core.util.meta import get_annotation_labels
+    arr = np.asarray(seg_img.array).reshape(shape_hw[0], shape_hw[1], -1)
+    info = get_annotation_labels(seg_img, fetch=False)
+    assert sorted(info) == sorted(ref_names)
+    return np.array([np.mean(arr[..., info[n]["value"] - 1] == ref_seg[..., i]) for i, n in enumerate(ref_names)])
+
+
+@pytest.mark.parametrize("plan_spacing", [1.25, 1.0])
+def test_config3_xray_single_channel(plan_spacing, tmp_path):
+    from totalsegmentator2d_b200 import nrrd, synth
+    from totalsegmentator2d_b200.tool import TS2D
+    torch.set_num_threads(os.cpu_count() or 1)
+    root = str(tmp_path)
+    labels = synth.TS2D_V2_GROUPS["ribs"]
+    synth.write_model_dir(root, "tsxr-v2-ep1000b2", "ribs", labels, synth.cs512_arch(), (512, 512), (plan_spacing, plan_spacing),
+                          channel_names=("xray",), seed=4242)
+    img = nrrd.read_nrrd(os.path.join(GOLDEN, "sample_chexpert.nrrd"))
+    assert img.GetSize() == (320, 320) and img.GetNumberOfComponentsPerPixel() == 1 and img.array.dtype == np.uint8
+    with TS2D(key="tsxr-v2-ep1000b2_ribs", models_root=root) as ts:
+        assert list(ts.models) == ["tsxr-v2-ep1000b2_ribs"] and ts.models["tsxr-v2-ep1000b2_ribs"].channels == {0: "xray"}
+        res = ts.predict(img)
+        seg = res.get_segmentation()
+        assert seg.GetSize() == (320, 320) and seg.GetNumberOfComponentsPerPixel() == 26
+        assert set(res.get_projection()) == {"ch0"}
+    om = oracle_models(root, "tsxr-v2-ep1000b2", ["ribs"])["tsxr-v2-ep1000b2_ribs"]
+    ref, logits, props = opipe.predict_model(np.asarray(img.array, dtype=np.float32)[None], img.GetSpacing(), om, mode="ideal", return_logits=True)
+    want_hw = (320, 320) if plan_spacing == 1.25 else (400, 400)
+    assert tuple(logits.shape[2:]) == want_hw
+    per = _per_label_agreement(seg, (320, 320), ref, om.label_names)
+    print(f"\nconfig 3 (X-ray, 1 channel, plan spacing {plan_spacing}): network grid {want_hw}, mean agreement {per.mean():.6f}, worst {per.min():.6f}")
+    assert per.mean() >= MASK_GATE
+
+
+def test_config4b_resampled_study(cs512_zoo):
+    """0.75 mm voxels -> plan spacing 1.5 mm: K3 in (order 3) and ts2d_threshold_logits out (order 1), five models, mirror TTA"""
+    import bench
+    from totalsegmentator2d_b200.image import Image
+    from totalsegmentator2d_b200.tool import TS2D
+    torch.set_num_threads(os.cpu_count() or 1)
+    root, groups = cs512_zoo
+    vol = bench.synthetic_volume(20260005)
+    sp = (0.75, 0.75, 0.75)
+    with TS2D(key="ts2d", models_root=root) as ts:
+        seg = ts.predict(Image(vol, sp, (0.0, 0.0, 0.0), np.eye(3).reshape(-1))).get_segmentation()
+    ref = opipe.predict_study(vol, sp, np.eye(3), oracle_models(root, bench.MODEL_KEY, groups), mode="ideal")
+    per = _per_label_agreement(seg, (1000, 512), ref["segmentation"], ref["names"])
+    print(f"\nconfig 4B (0.75 mm -> 500 x 256 -> back): mean agreement {per.mean():.6f}, worst {per.min():.6f}")
+    assert seg.GetSize() == (512, 1, 1000) and per.mean() >= MASK_GATE
+
+
+def test_config4_permuted_flipped_direction(cs512_zoo):
+    """the stored array is [x][z][y]-like with two flipped axes; TS2D.predict folds reorient_image('RAI') into the projection
+    kernel's addressing, the oracle reorients explicitly (reference ts2d/tool.py:154, core/util/image.py:32-43)"""
+    import bench
+    from totalsegmentator2d_b200.image import Image
+    from totalsegmentator2d_b200.tool import TS2D
+    torch.set_num_threads(os.cpu_count() or 1)
+    root, groups = cs512_zoo
+    D = np.array([[0.0, 0.0, 1.0], [-1.0, 0.0, 0.0], [0.0, -1.0, 0.0]])
+    perm, flip = geometry.orientation_remap(D, "RAI")
+    assert tuple(perm) != (0, 1, 2) and any(flip)
+    want = (700, 40, 512)                                    # RAI [z][y][x]: image 700 x 512 (2 tiles), 40 coronal slices
+    import itertools
+    shape = next(s for s in itertools.permutations(want) if geometry.reorient_array(np.empty(s, np.int8), perm, flip).shape == want)
+    vol = bench.synthetic_volume(20260009, shape)
+    img = Image(vol, (1.5, 1.5, 1.5), (3.0, -2.0, 1.0), D.reshape(-1))
+    with TS2D(key="ts2d", models_root=root) as ts:
+        res = ts.predict(img)
+        seg = res.get_segmentation()
+        projs = {k: np.asarray(v.array).reshape(700, 512) for k, v in res.get_projection().items()}
+    ref = opipe.predict_study(vol, (1.5, 1.5, 1.5), D, oracle_models(root, bench.MODEL_KEY, groups), mode="ideal")
+    assert np.array_equal(projs["max"], ref["projections"]["max"]) and np.array_equal(projs["mean"], ref["projections"]["mean"])
+    per = _per_label_agreement(seg, (700, 512), ref["segmentation"], ref["names"])
+    print(f"\nconfig 4 permuted + flipped study {shape} -> RAI {want}: mean agreement {per.mean():.6f}, worst {per.min():.6f}")
+    assert seg.GetSize() == (512, 1, 700) and per.mean() >= MASK_GATE
+
+
+@pytest.mark.parametrize("img_spacing", [1.5, 1.0])
+def test_operator_seam_replays_reference_worker(img_spacing, tmp_path):
+    """reference ts2d/core/inference/prediction_worker.py:177-224, literally, against the duck-typed predictor + the free function
+    export_prediction_from_logits; the written file is compared with the oracle's mask (spacing 1.0 exercises both resamplings)"""
+    from totalsegmentator2d_b200 import nrrd, synth
+    from totalsegmentator2d_b200.core.inference.export import export_prediction_from_logits
+    from totalsegmentator2d_b200.core.inference.predictor import B200nnUNetPredictor
+    from totalsegmentator2d_b200.image import Image
+    root = str(tmp_path / "zoo")
+    labels = synth.TS2D_V2_GROUPS["cardiac"][:9]
+    synth.write_model_dir(root, "ts2d-v2-ep4000b2", "cardiac", labels, synth.make_arch_kwargs([32, 64, 128, 128]), (128, 128), (1.5, 1.5), seed=77)
+    tdir = opipe.find_training_dir(os.path.join(root, "ts2d-v2-ep4000b2_cardiac", "r001"))
+    rng = np.random.default_rng(3)
+    chw = rng.normal(0, 300, size=(2, 150, 110)).astype(np.float32)
+    chw[:, :9] = 0
+    chw[:, :, 100:] = 0                                       # zero borders: crop_to_nonzero really crops
+    fin = str(tmp_path / "case_0000.nrrd")
+    nrrd.write_nrrd(Image(np.moveaxis(chw, 0, -1), (img_spacing, img_spacing), (5.0, 6.0), None, is_vector=True), fin, True)
+    ofile = str(tmp_path / "out" / "case.nrrd")
+
+    predictor = B200nnUNetPredictor(tile_step_size=0.5, use_mirroring=True, verbose=False, allow_tqdm=False,
+                                    device=torch.device("cuda", 0), perform_everything_on_device=True)
+    predictor.initialize_from_trained_model_folder(tdir, [0], "checkpoint_final.pth")
+    assert "nnUNetPredictor" in type(predictor).__name__                      # prediction_worker.py:103,111
+    # ---- prediction_worker.py:178-224 ----
+    ofile_truncated, ofile_ext = os.path.splitext(ofile)
+    assert predictor.dataset_json["file_ending"] == ofile_ext
+    os.makedirs(os.path.dirname(ofile), exist_ok=True)
+    preprocessor = predictor.configuration_manager.preprocessor_class(verbose=predictor.verbose)
+    data, _, data_properties = preprocessor.run_case([fin], None, predictor.plans_manager, predictor.configuration_manager, predictor.dataset_json)
+    assert isinstance(data, np.ndarray) and data.dtype == np.float32 and data.ndim == 4 and data.shape[1] == 1
+    data = torch.from_numpy(data).to(dtype=torch.float32, memory_format=torch.contiguous_format)
+    if predictor.device.type == "cuda":
+        data.pin_memory()
+    prediction = predictor.predict_logits_from_preprocessed_data(data).cpu()
+    export_prediction_from_logits(prediction, data_properties, predictor.configuration_manager, predictor.plans_manager,
+                                  predictor.dataset_json, ofile_truncated, False)
+    # ---- what the parent then reads back (nnu.py:221) ----
+    seg = nrrd.read_nrrd(ofile)
+    assert seg.GetSize() == (110, 150) and seg.GetNumberOfComponentsPerPixel() == 9 and seg.GetSpacing() == (img_spacing, img_spacing)
+    assert seg.GetOrigin() == (5.0, 6.0)
+    om = opipe.OracleModel(tdir)
+    ref, logits, props = opipe.predict_model(chw, (img_spacing, img_spacing), om, mode="ideal", return_logits=True)
+    assert props["bbox_used_for_cropping"] == data_properties["bbox_used_for_cropping"] == [[0, 1], [9, 150], [0, 100]]
+    assert tuple(prediction.shape) == tuple(logits.shape)
+    agree = float(np.mean(np.asarray(seg.array) == ref))
+    err = float(np.abs(prediction.numpy() - logits).max())
+    print(f"\noperator seam, image spacing {img_spacing}: logits {tuple(prediction.shape)} max |dlogit| {err:.5f}, written mask agreement {agree:.6f}")
+    assert agree >= MASK_GATE
+    predictor.close()

@@ -115,6 +115,26 @@ def test_save_writes_reference_file_names(zoo, tmp_path):
         assert os.path.exists(os.path.join(str(tmp_path), fn)), fn
     seg = nrrd.read_nrrd(os.path.join(str(tmp_path), f"{s}.seg.nrrd"))
     assert seg.GetSize() == (53, 1, 133) and seg.HasMetaDataKey("Segment0_Name") and seg.GetMetaData("Segment0_LabelValue") == "1"
+    # the CONTENT of the files on disk, read back and compared per label NAME with the oracle (reference tool.py:235-311,
+    # meta.py:172-240): merged mask, every per-group mask, both projections
+    from totalsegmentator2d_b200.core.util.meta import get_annotation_labels
+    src = nrrd.read_nrrd(os.path.join(GOLDEN, "sample_s0521.nrrd"))
+    ref = opipe.predict_study(np.asarray(src.array), src.GetSpacing(), src.direction_matrix(), _oracle_models(root, groups), mode="ideal")
+    info = get_annotation_labels(seg, fetch=False)
+    arr = np.asarray(seg.array).reshape(133, 53, -1)
+    assert [v["name"] for v in sorted(info.values(), key=lambda v: v["value"])] == ref["names"]
+    per = [np.mean(arr[..., info[n]["value"] - 1] == ref["segmentation"][..., i]) for i, n in enumerate(ref["names"])]
+    assert np.mean(per) >= 0.999, np.mean(per)
+    for g in groups:
+        gs = nrrd.read_nrrd(os.path.join(str(tmp_path), f"{s}-{g}.seg.nrrd"))
+        ga = np.asarray(gs.array).reshape(133, 53, -1)
+        ginfo = get_annotation_labels(gs, fetch=False)
+        want = ref["models"][f"ts2d-v2-ep4000b2_{g}"]
+        assert [v["name"] for v in sorted(ginfo.values(), key=lambda v: v["value"])] == list(groups[g])     # per-model files keep the label order
+        assert np.mean(ga == want) >= 0.999
+    for ch in ("max", "mean"):
+        pr = nrrd.read_nrrd(os.path.join(str(tmp_path), f"{s}_{ch}.nrrd"))
+        assert np.array_equal(np.asarray(pr.array).reshape(133, 53), ref["projections"][ch])
 
 
 def test_predict_batch_pipeline_equals_predict(zoo):

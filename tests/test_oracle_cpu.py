@@ -226,3 +226,55 @@ def test_c_abi_library_exports_every_declared_symbol():
     if not torch.cuda.is_available():
         with pytest.raises(_lib.TS2DError, match="no CUDA device"):
             _lib.load(check_device=True)
+
+
+def test_nifti_and_metaimage_readers_round_trip(tmp_path):
+    """reference ts2d/main.py:25 whitelists nii / nii.gz / mha / mhd and reads them with sitk.ReadImage (image.py:225-238): the
+    restated readers must return the same [z][y][x] array and LPS geometry for every writer variant, incl. an oblique direction,
+    a flipped axis (negative determinant -> qfac = -1), big-endian data, scl_slope / scl_inter and detached .mhd data."""
+    import gzip
+    import struct
+    from totalsegmentator2d_b200 import formats, nrrd
+    from totalsegmentator2d_b200.core.util.image import read_image
+    from totalsegmentator2d_b200.image import Image
+    rng = np.random.default_rng(5)
+    arr = rng.integers(-1024, 3071, size=(7, 5, 9)).astype(np.int16)
+    th = 0.3
+    rot = np.array([[np.cos(th), -np.sin(th), 0], [np.sin(th), np.cos(th), 0], [0, 0, 1.0]])
+    for D in (np.eye(3), np.diag([-1.0, -1.0, 1.0]), rot, rot @ np.diag([1.0, -1.0, 1.0]), np.eye(3)[[2, 0, 1]]):
+        img = Image(arr, (0.7, 1.5, 2.25), (10.0, -20.0, 30.5), D.reshape(-1))
+        for ext in ("nii", "nii.gz", "mha", "mhd", "nrrd"):
+            fp = str(tmp_path / f"v.{ext}")
+            (nrrd.write_nrrd(img, fp, True) if ext == "nrrd" else formats.write_any(img, fp))
+            back = read_image(fp)
+            assert np.array_equal(back.array, arr) and back.array.dtype == np.int16, ext
+            assert np.allclose(back.GetSpacing(), img.GetSpacing(), atol=1e-5), (ext, back.GetSpacing())
+            assert np.allclose(back.GetOrigin(), img.GetOrigin(), atol=1e-4), (ext, back.GetOrigin())
+            assert np.allclose(back.direction_matrix(), D, atol=1e-5), (ext, back.direction_matrix())
+    # sform-only, big-endian, scaled NIfTI written by hand: x fastest, RAS affine diag(2,3,4) + offset -> LPS flips x and y
+    a = np.arange(2 * 3 * 4, dtype=">i2").reshape(4, 3, 2)
+    hdr = bytearray(352)
+    struct.pack_into(">i", hdr, 0, 348)
+    struct.pack_into(">8h", hdr, 40, 3, 2, 3, 4, 1, 1, 1, 1)
+    struct.pack_into(">2h", hdr, 70, 4, 16)
+    struct.pack_into(">8f", hdr, 76, 1, 2, 3, 4, 0, 0, 0, 0)
+    struct.pack_into(">3f", hdr, 108, 352.0, 0.5, -3.0)
+    struct.pack_into(">2h", hdr, 252, 0, 1)
+    struct.pack_into(">12f", hdr, 280, 2, 0, 0, 5, 0, 3, 0, 6, 0, 0, 4, 7)
+    hdr[344:348] = b"n+1\0"
+    fp = str(tmp_path / "be.nii.gz")
+    with gzip.open(fp, "wb") as f:
+        f.write(bytes(hdr) + a.tobytes())
+    back = read_image(fp)
+    assert back.array.dtype == np.float32 and np.allclose(back.array, a.astype(np.float64) * 0.5 - 3.0)
+    assert np.allclose(back.GetSpacing(), (2, 3, 4)) and np.allclose(back.GetOrigin(), (-5, -6, 7))
+    assert np.allclose(back.direction_matrix(), np.diag([-1.0, -1.0, 1.0]))
+    # vector MetaImage (2-D, 3 channels) and the NRRD metadata escape round trip (backslash followed by 'n')
+    v = rng.integers(0, 255, size=(6, 4, 3)).astype(np.uint8)
+    vi = Image(v, (1.0, 2.0), (0.0, 1.0), None, is_vector=True)
+    formats.write_any(vi, str(tmp_path / "vec.mha"))
+    vb = read_image(str(tmp_path / "vec.mha"))
+    assert vb.is_vector and np.array_equal(vb.array, v) and vb.GetSize() == (4, 6)
+    vi.SetMetaData("k", "a\\nb\nc\\\\")
+    nrrd.write_nrrd(vi, str(tmp_path / "m.nrrd"), False)
+    assert nrrd.read_nrrd(str(tmp_path / "m.nrrd")).GetMetaData("k") == "a\\nb\nc\\\\"

@@ -82,6 +82,7 @@ _PROTOS = {
     "ts2d_unet_flops": (C.c_double, [_vp, _i]),
     "ts2d_unet_set_profiling": (_i, [_vp, _i]),
     "ts2d_unet_last_conv_ms": (C.c_double, [_vp]),
+    "ts2d_unet_last_forward_ms": (C.c_double, [_vp]),
     "ts2d_unet_profile_count": (_i, [_vp]),
     "ts2d_unet_profile_entry": (_i, [_vp, _i, C.c_char_p, _i, _ip, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "ts2d_unet_destroy": (_i, [_vp]),

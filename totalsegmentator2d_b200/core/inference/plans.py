@@ -103,7 +103,13 @@ def foreground_labels(dataset_json: dict) -> List[str]:
     def key(kv):
         v = kv[1]
         return int(v) if not isinstance(v, (list, tuple)) else int(v[0])
-    return [k for k, v in sorted(labels.items(), key=key) if k != "background"]
+    vals = [key(kv) for kv in labels.items()]
+    # the reference names channel c by the (c+1)-th KEY of dataset.json (wrapper.py:270-271: dict(enumerate(labels.keys()))),
+    # nnU-Net orders the heads by label VALUE: both agree only when the file lists background = 0 first and the values ascend
+    if vals != list(range(len(vals))) or next(iter(labels)) != "background":
+        raise RuntimeError("dataset.json labels must be listed as background = 0 followed by 1, 2, ... in ascending order "
+                           "(found values {})".format(vals))
+    return [k for k, v in labels.items() if k != "background"]
 
 
 def channel_names(dataset_json: dict) -> Dict[int, str]:

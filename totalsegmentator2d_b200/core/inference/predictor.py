@@ -123,6 +123,11 @@ class B200nnUNetPredictor:
 
     def manual_initialization(self, plans: dict, configuration: str, dataset_json: dict, state_dicts: Sequence[dict], inference_allowed_mirroring_axes):
         self.close()
+        for key in ("transpose_forward", "transpose_backward"):
+            t = [int(v) for v in plans.get(key, [0, 1, 2])]
+            if t != sorted(t):
+                raise L.TS2DError(f"plans.json {key} = {t}: only identity transposes are implemented (a 2-D configuration of a "
+                                  "SimpleITKIO dataset never has another one)")
         self.plans_manager = PlansManager(plans)
         self.configuration_manager = self.plans_manager.get_configuration(configuration)
         self.dataset_json = dataset_json
@@ -204,6 +209,10 @@ class B200nnUNetPredictor:
 
     def last_conv_ms(self) -> float:
         return sum(float(self._lib.ts2d_unet_last_conv_ms(h)) for h in self._handles)
+
+    def last_forward_ms(self) -> float:
+        """all launches of the last profiled forward (convs + norm-apply + split-K finish)"""
+        return sum(float(self._lib.ts2d_unet_last_forward_ms(h)) for h in self._handles)
 
     def layer_profile(self, fold: int = 0):
         """[(name, kind, ms, algorithmic flops, algorithmic bytes)] of the last profiled forward"""

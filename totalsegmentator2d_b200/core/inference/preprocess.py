@@ -109,7 +109,7 @@ class B200Preprocessor:
             arrs.append(a)
             sp = [s for s, n in zip(im.GetSpacing(), im.GetSize()) if n > 1] if im.GetDimension() > 2 else list(im.GetSpacing())
             spacing_xy = sp[:2]
-            geo = {"spacing": im.GetSpacing(), "origin": im.GetOrigin(), "direction": im.GetDirection()}
+            geo = {"spacing": im.GetSpacing(), "origin": im.GetOrigin(), "direction": im.GetDirection(), "size": im.GetSize()}
         chw = np.concatenate(arrs, axis=0).astype(np.float32)
         dev = torch.from_numpy(np.ascontiguousarray(chw)).cuda()
         data, props = self.run_case_device(dev, spacing_xy, plans_manager, configuration_manager, dataset_json)

@@ -148,7 +148,10 @@ def read_image(fp: str) -> Image:
     low = fp.lower()
     if low.endswith(".nrrd"):
         return read_nrrd(fp)
-    raise RuntimeError("unsupported image format for {} (this build reads .nrrd; .nii/.mha readers are the next row of the scope table)".format(fp))
+    if low.endswith((".nii", ".nii.gz", ".mha", ".mhd")):
+        from ...formats import read_any
+        return read_any(fp)
+    raise RuntimeError("unsupported image format for {} (supported: nrrd, nii, nii.gz, mha, mhd)".format(fp))
 
 
 def reduce_dimensions(img: Image, strategy=None, min=None) -> Image:

@@ -1168,11 +1168,11 @@ extern "C" int ts2d_unet_set_profiling(ts2d_unet *u, int enable) {
     return TS2D_OK;
 }
 
-extern "C" double ts2d_unet_last_conv_ms(ts2d_unet *u) {
+static double prof_sum_ms(ts2d_unet *u, bool all_kinds) {
     if (!u || !u->profiling) return -1.0;
     double total = 0.0;
     for (int i = 0; i < u->prof_used; ++i) {
-        if (u->prof_entries[i].kind == 2) continue;     // norm-apply passes are not conv time
+        if (!all_kinds && u->prof_entries[i].kind == 2) continue;     // norm-apply / split-K finish passes are not conv time
         if (cudaEventSynchronize(u->prof_events[i].second) != cudaSuccess) return -1.0;
         float ms = 0.f;
         if (cudaEventElapsedTime(&ms, u->prof_events[i].first, u->prof_events[i].second) != cudaSuccess) return -1.0;
@@ -1180,6 +1180,8 @@ extern "C" double ts2d_unet_last_conv_ms(ts2d_unet *u) {
     }
     return total;
 }
+extern "C" double ts2d_unet_last_conv_ms(ts2d_unet *u) { return prof_sum_ms(u, false); }
+extern "C" double ts2d_unet_last_forward_ms(ts2d_unet *u) { return prof_sum_ms(u, true); }
 
 extern "C" int ts2d_unet_profile_count(const ts2d_unet *u) { return (u && u->profiling) ? u->prof_used : 0; }
 

@@ -67,7 +67,7 @@ def read_header(buf: bytes) -> Tuple[Dict[str, str], Dict[str, str], int]:
             continue
         if ":=" in line:
             k, v = line.split(":=", 1)
-            meta[k] = v.replace("\\n", "\n").replace("\\\\", "\\")
+            meta[k] = re.sub(r"\\(.)", lambda m: "\n" if m.group(1) == "n" else m.group(1), v)     # one left-to-right pass
         elif ":" in line:
             k, v = line.split(":", 1)
             fields[k.strip().lower()] = v.strip()

@@ -307,8 +307,13 @@ class TS2D:
         on its way to the host) while study i computes and the mask of study i-1 is downloaded and wrapped on the host; the
         host never waits for the GPU between the upload and the U-Nets.  Results come out in input order."""
         staged, pending = [], []
+        failure = None
         for inp in inputs:
-            staged.append(self._stage_upload(inp, collapse, merge))
+            try:
+                staged.append(self._stage_upload(inp, collapse, merge))
+            except Exception as ex:       # an unreadable input: the studies already in flight are finished and yielded first
+                failure = ex
+                break
             if len(staged) > max(0, lookahead):
                 pending.append(self._stage_compute(staged.pop(0)))
             if len(pending) >= max(1, depth):
@@ -319,6 +324,8 @@ class TS2D:
                 yield self._finish(pending.pop(0))
         while pending:
             yield self._finish(pending.pop(0))
+        if failure is not None:
+            raise failure
 
     def _streams(self):
         if getattr(self, "_h2d_stream", None) is None:
@@ -569,9 +576,13 @@ class TS2D:
                 return base if key is None else f"{base}-{key}"
 
             def _write(img, filepath):
-                if ext.lower() != "nrrd":
-                    raise RuntimeError(f"unsupported export format '{ext}' (this build writes .nrrd)")
-                write_nrrd(img, filepath, True)
+                if ext.lower() == "nrrd":
+                    write_nrrd(img, filepath, True)
+                elif ext.lower() in ("nii", "nii.gz", "mha", "mhd"):
+                    from .formats import write_any
+                    write_any(img, filepath)
+                else:
+                    raise RuntimeError(f"unsupported export format '{ext}' (supported: nrrd, nii, nii.gz, mha, mhd)")
 
             def _export_image(img, base_name, suffix="", labels=False):
                 if "file" in content:
