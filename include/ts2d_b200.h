@@ -152,6 +152,9 @@ int ts2d_unet_blend_head(ts2d_unet *u, const int *tile_yx_host, int T, int M, in
                          int pad_top, int pad_left, int h, int w, const float *gaussian_dev,
                          float *logits_dev, uint8_t *mask_dev, int H0, int W0, int h0, int w0,
                          int ch_off, int ch_total, uint8_t *present_dev, ts2d_stream stream);
+/* 1 when ts2d_unet_blend_head writes the model's channel window of every pixel of the mask (zeros outside the crop box): the
+ * caller need not clear the merged mask first (saves a 60 MB memset per study) */
+int ts2d_unet_blend_covers_image(const ts2d_unet *u);
 /* export when the plan resamples: logits float32 [heads][h][w] -> order-1 resize to (h2,w2) -> >0 -> mask */
 int ts2d_threshold_logits(const float *logits_dev, int heads, int h, int w, int h2, int w2,
                           uint8_t *mask_dev, int H0, int W0, int h0, int w0, int ch_off, int ch_total,

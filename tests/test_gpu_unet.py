@@ -204,3 +204,36 @@ def test_multicast_pairs_bit_identical(precision, monkeypatch):
         outs.append((p.predict_tile_logits(xd).cpu(), p.forward_debug(xd, "dec0.0", (128, 16, 24)).cpu()))
         p.close()
     assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+
+
+@pytest.mark.parametrize("precision", ["fp16", "bf16"])
+@pytest.mark.parametrize("feats,mirror", [([32, 64, 128], True), ([16, 32, 64], False), ([64, 64], True)])
+def test_blend_v2_equals_v1(precision, feats, mirror, monkeypatch):
+    """blend_head_v2_kernel (F/8 lanes per pixel, head through shared memory, whole-image grid that also writes the zeros outside the
+    crop box) against blend_head_kernel: logits equal up to the re-association of the head's fp32 dot product, mask bytes equal
+    wherever |logit| is not tiny, and the v2 mask needs no memset (the buffer starts as 0xFF)."""
+    from totalsegmentator2d_b200 import ops
+    p, sd, spec = _make(feats, (64, 64), heads=7, precision=precision, seed=17, mirror=mirror)
+    g = torch.Generator().manual_seed(2)
+    data = torch.randn(2, 100, 150, generator=g).cuda()
+    x, layout = p.make_tiles(data)
+    outs = {}
+    for v2 in ("0", "1"):
+        monkeypatch.setenv("TS2D_BLEND_V2", v2)
+        logits = torch.empty((7, 100, 150), dtype=torch.float32, device="cuda")
+        p.run_tiles(x, layout, (100, 150), logits=logits)
+        mask = torch.full((120, 170, 20), 255 if v2 == "1" else 0, dtype=torch.uint8, device="cuda")
+        present = torch.zeros(20, dtype=torch.uint8, device="cuda")
+        p.run_tiles(x, layout, (100, 150), mask=mask, crop_origin=(11, 13), ch_off=5, present=present)
+        outs[v2] = (logits.cpu(), mask.cpu(), present.cpu())
+    assert p.blend_covers_image
+    la, lb = outs["0"][0], outs["1"][0]
+    assert float((la - lb).abs().max()) <= 2e-5, float((la - lb).abs().max())
+    ma, mb = outs["0"][1], outs["1"][1]
+    assert torch.equal(mb[..., :5], torch.full_like(mb[..., :5], 255)) and torch.equal(mb[..., 12:], torch.full_like(mb[..., 12:], 255))     # other models' windows untouched
+    win = mb[..., 5:12]
+    assert int(win[:11].sum()) == 0 and int(win[111:].sum()) == 0 and int(win[:, :13].sum()) == 0 and int(win[:, 163:].sum()) == 0      # zeros outside the crop box
+    sure = (la.abs() > 1e-4).permute(1, 2, 0)
+    assert torch.equal(win[11:111, 13:163][sure], ma[11:111, 13:163, 5:12][sure])
+    assert torch.equal(win[11:111, 13:163], (lb > 0).permute(1, 2, 0).to(torch.uint8))
+    assert torch.equal(outs["0"][2], outs["1"][2])

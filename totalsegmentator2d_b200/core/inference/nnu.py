@@ -180,8 +180,9 @@ class NNUDeviceModel(NNUModel):
         separate streams."""
         p = self.predictor
         C, H, W = img_dev.shape
-        if mask is None:
-            mask = torch.zeros((H, W, p.num_heads), dtype=torch.uint8, device=img_dev.device)
+        own_mask = mask is None
+        if own_mask:
+            mask = torch.empty((H, W, p.num_heads), dtype=torch.uint8, device=img_dev.device)
         key = self.preprocess_key() + tuple(cache_key)
         entry = cache.get(key) if cache is not None else None
         if entry is None:
@@ -196,7 +197,11 @@ class NNUDeviceModel(NNUModel):
         shape, props, x, layout = entry
         (_, (h0, h1), (w0, w1)) = props["bbox_used_for_cropping"]
         hw = (int(shape[1]), int(shape[2]))
-        if hw == (h1 - h0, w1 - w0):
+        direct = hw == (h1 - h0, w1 - w0)
+        if not (direct and p.blend_covers_image):
+            # this path only writes the crop box: clear the model's channel window first
+            (mask if own_mask else mask[..., ch_off:ch_off + p.num_heads]).zero_()
+        if direct:
             p.run_tiles(x, layout, hw, mask=mask, crop_origin=(h0, w0), ch_off=ch_off, present=present)
         else:
             from ... import ops

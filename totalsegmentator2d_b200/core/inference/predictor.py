@@ -194,6 +194,11 @@ class B200nnUNetPredictor:
             mask |= 1 << int(a)
         return mask
 
+    @property
+    def blend_covers_image(self) -> bool:
+        """run_tiles(mask=...) writes this model's channel window of every mask pixel (zeros outside the crop box)"""
+        return len(self._handles) == 1 and bool(self._lib.ts2d_unet_blend_covers_image(self._handles[0]))
+
     def workspace_bytes(self) -> int:
         return sum(int(self._lib.ts2d_unet_workspace_bytes(h)) for h in self._handles)
 

@@ -1,0 +1,199 @@
+// K8/K9 (16-bit feature path): mirror-TTA average + Gaussian-weighted tile blend + 1x1 segmentation head + threshold / paste,
+// one launch per group model.  Replaces blend_head_kernel for fp16 / bf16 features (that kernel stays for fp32 and as the
+// parity reference): same arithmetic order per output value up to fp32 re-association of the head's dot product.
+//
+// Reference: nnUNetPredictor.predict_sliding_window_return_logits + _internal_maybe_mirror_and_predict (mirror average,
+// Gaussian accumulate / normalise) and export_prediction_from_logits (sigmoid > 0.5 == logit > 0, paste at the crop box) as
+// reached from reference ts2d/core/inference/prediction_worker.py:209,215-221.
+//
+// Why a second kernel (ncu of blend_head_kernel, profiles/r02_blend_ncu.txt): one thread per pixel read its 64-byte feature
+// vector as four 16-byte loads at a 64-byte lane stride with L1 bypass, so every 32-byte sector crossed the L2 -> SM path twice,
+// and the 32 x heads matvec + 16 fp32-pair accumulators + 16 staged 16-byte loads per thread left 128-thread blocks at ~25 %
+// occupancy.  Here:
+//   phase 1  F/8 adjacent lanes own one pixel (8 channels each): a warp's load instruction covers whole 128-byte lines; every
+//            lane keeps 8 fp32 accumulators; InstanceNorm {scale, shift} of all T*M images sit in shared memory;
+//   phase 2  the blended fp32 features go through shared memory ([pixel][F + 4] floats, conflict-free 16-byte rows) and thread
+//            (pixel, head group) computes ceil(heads / G) logits with the head weights as warp-broadcast 16-byte loads;
+//   phase 3  mask bytes leave through shared memory as consecutive bytes of each pixel's channel window.
+// The grid covers the WHOLE output image: pixels outside the crop box get zeros in this model's channel window, so the
+// 60 MB memset of the merged mask per study is gone (mask_covers_image = 1).
+#pragma once
+#include "conv_tc.cuh"
+#include "unet_kernels.cuh"
+
+namespace ts2d {
+
+constexpr int kBlend2Threads = 256;
+
+template <typename T, int F, int CAP>
+__global__ void __launch_bounds__(kBlend2Threads, F <= 32 ? 4 : 2) blend_head_v2_kernel(const BlendParams p, const __grid_constant__ TileListT<CAP> tl, int full_h, int full_w, int ss_smem) {
+    static_assert(F % 8 == 0 && F <= 64, "blend_head_v2_kernel: F must be 8, 16, 32 or 64");
+    constexpr int LPP = F / 8;                       // lanes per pixel
+    constexpr int PPB = kBlend2Threads / LPP;        // pixels per block
+    constexpr int G = LPP;                           // head groups in phase 2 (PPB * G == 256)
+    constexpr int FS = F + 4;                        // padded feature row (floats): 16-byte aligned, conflict-free float4 reads
+    extern __shared__ __align__(16) float s_mem[];
+    // layout: head_w [heads][F] | head_b [heads] (padded to 4) | feat [PPB][FS] | ss [T*M][F][2] (scale, shift; only when feat_ss) |
+    //         pixel base offsets [PPB] (long long) | mask bytes [PPB][heads] | any flags [heads] (int)
+    const int heads = p.heads;
+    const int hb_pad = (heads + 3) & ~3;
+    float *s_w = s_mem;
+    float *s_b = s_w + heads * F;
+    float *s_feat = s_b + hb_pad;
+    float *s_ss = s_feat + PPB * FS;
+    const int n_img = p.T * p.M;
+    long long *s_base = reinterpret_cast<long long *>(s_ss + ((p.feat_ss && ss_smem) ? n_img * F * 2 : 0));
+    uint8_t *s_mask = reinterpret_cast<uint8_t *>(s_base + PPB);
+    int *s_any = reinterpret_cast<int *>(s_mask + ((PPB * heads + 15) & ~15));
+
+    const int tid = threadIdx.x;
+    for (int i = tid; i < heads * F; i += kBlend2Threads) s_w[i] = p.head_w[i];
+    for (int i = tid; i < hb_pad; i += kBlend2Threads) s_b[i] = (i < heads && p.head_b) ? p.head_b[i] : 0.f;
+    for (int i = tid; i < heads; i += kBlend2Threads) s_any[i] = 0;
+    if (p.feat_ss && ss_smem) {
+        // norm_finalize_kernel pair layout {sc[2j], sc[2j+1], sh[2j], sh[2j+1]} -> [img][c] scale, [img][F + c] shift
+        for (int i = tid; i < n_img * F; i += kBlend2Threads) {
+            const int img = i / F, c = i - img * F;
+            const float *src = p.feat_ss + (long long)img * F * 2 + (c >> 1) * 4 + (c & 1);
+            s_ss[img * 2 * F + c] = src[0];
+            s_ss[img * 2 * F + F + c] = src[2];
+        }
+    }
+    __syncthreads();
+
+    // ---------------- phase 1: blend ----------------
+    const int pl = tid / LPP, q = tid % LPP;                    // local pixel, channel block (8 channels)
+    const long long npix_full = (long long)full_h * full_w;
+    const long long gp = (long long)blockIdx.x * PPB + pl;      // pixel of the full output image (mask space) or of the crop (no mask)
+    const bool in_img = gp < npix_full;
+    const int fy = in_img ? (int)(gp / full_w) : 0, fx = in_img ? (int)(gp % full_w) : 0;
+    // crop coordinates (the network's grid): the mask window starts at (h0, w0)
+    const int y = fy - (p.mask ? p.h0 : 0), x = fx - (p.mask ? p.w0 : 0);
+    const bool active = in_img && y >= 0 && y < p.h && x >= 0 && x < p.w;
+    const int yp = y + p.pad_top, xp = x + p.pad_left;
+    float acc[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+    float wsum = 0.f;
+    const T *feat = reinterpret_cast<const T *>(p.feat);
+    const float inv_m = 1.0f / (float)p.M;
+    const float slope = p.slope;
+    if (active) {
+        for (int t = 0; t < p.T; ++t) {
+            const int ly = yp - tl.yx[t][0], lx = xp - tl.yx[t][1];
+            if (ly < 0 || ly >= p.Ph || lx < 0 || lx >= p.Pw) continue;
+            const float g = __ldg(p.gauss + ly * p.Pw + lx);
+            wsum += g;
+            const float gm = g * inv_m;
+            uint4 v[4];
+#pragma unroll
+            for (int m = 0; m < 4; ++m) {
+                if (m < p.M) {
+                    bool fh = false, fw = false;
+                    if (p.mirror_mask == 3) { fh = (m & 1) != 0; fw = (m & 2) != 0; }
+                    else if (p.mirror_mask == 1) fh = (m == 1);
+                    else if (p.mirror_mask == 2) fw = (m == 1);
+                    const int sy = fh ? p.Ph - 1 - ly : ly, sx = fw ? p.Pw - 1 - lx : lx;
+                    v[m] = __ldg(reinterpret_cast<const uint4 *>(feat + (((long long)(t * p.M + m) * p.Ph + sy) * p.Pw + sx) * F + q * 8));
+                }
+            }
+#pragma unroll
+            for (int m = 0; m < 4; ++m) {
+                if (m < p.M) {
+                    const uint32_t *w = reinterpret_cast<const uint32_t *>(&v[m]);
+                    float f[8];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) { const float2 e = unpack2<T>(w[j]); f[2 * j] = e.x; f[2 * j + 1] = e.y; }
+                    if (p.feat_ss) {
+                        float scv[8], shv[8];
+                        if (ss_smem) {
+                            const float4 *sc = reinterpret_cast<const float4 *>(s_ss + (t * p.M + m) * 2 * F + q * 8);
+                            const float4 *sh = reinterpret_cast<const float4 *>(s_ss + (t * p.M + m) * 2 * F + F + q * 8);
+                            const float4 a0 = sc[0], a1 = sc[1], b0 = sh[0], b1 = sh[1];
+                            scv[0] = a0.x; scv[1] = a0.y; scv[2] = a0.z; scv[3] = a0.w; scv[4] = a1.x; scv[5] = a1.y; scv[6] = a1.z; scv[7] = a1.w;
+                            shv[0] = b0.x; shv[1] = b0.y; shv[2] = b0.z; shv[3] = b0.w; shv[4] = b1.x; shv[5] = b1.y; shv[6] = b1.z; shv[7] = b1.w;
+                        } else {
+                            // too many tiles for shared memory: the pair layout {sc, sc, sh, sh} straight from global memory (L1 hits)
+                            const float4 *ss = reinterpret_cast<const float4 *>(p.feat_ss) + (long long)(t * p.M + m) * (F / 2) + q * 4;
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                const float4 c4 = __ldg(ss + j);
+                                scv[2 * j] = c4.x; scv[2 * j + 1] = c4.y; shv[2 * j] = c4.z; shv[2 * j + 1] = c4.w;
+                            }
+                        }
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) {
+                            const float yv = fmaf(f[k], scv[k], shv[k]);
+                            f[k] = yv > 0.f ? yv : yv * slope;
+                        }
+                    }
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) acc[k] = fmaf(gm, f[k], acc[k]);
+                }
+            }
+        }
+    }
+    {
+        const float inv = active ? 1.0f / wsum : 0.f;
+        float4 *dst = reinterpret_cast<float4 *>(s_feat + pl * FS + q * 8);
+        dst[0] = make_float4(acc[0] * inv, acc[1] * inv, acc[2] * inv, acc[3] * inv);
+        dst[1] = make_float4(acc[4] * inv, acc[5] * inv, acc[6] * inv, acc[7] * inv);
+    }
+    if (q == 0) s_base[pl] = in_img ? (active ? 1LL : 0LL) | (((long long)fy * p.W0 + fx) * p.ch_total + p.ch_off) << 1 : -1LL;
+    __syncthreads();
+
+    // ---------------- phase 2: head ----------------
+    const int hp = tid % PPB, hg = tid / PPB;                   // pixel, head group (a warp shares hg: weight loads broadcast)
+    const int hpg = (heads + G - 1) / G;                        // heads per group
+    const int c_lo = hg * hpg, c_hi = min(heads, c_lo + hpg);
+    const long long hbase = s_base[hp];
+    const bool h_in = hbase >= 0, h_act = h_in && (hbase & 1);
+    {
+        float fv[F];
+        const float4 *fr = reinterpret_cast<const float4 *>(s_feat + hp * FS);
+#pragma unroll
+        for (int k = 0; k < F / 4; ++k) { const float4 t4 = fr[k]; fv[4 * k] = t4.x; fv[4 * k + 1] = t4.y; fv[4 * k + 2] = t4.z; fv[4 * k + 3] = t4.w; }
+        // crop-space coordinates of this thread's pixel (logits output)
+        const long long gp2 = (long long)blockIdx.x * PPB + hp;
+        const int fy2 = (int)(gp2 / full_w), fx2 = (int)(gp2 % full_w);
+        const int y2 = fy2 - (p.mask ? p.h0 : 0), x2 = fx2 - (p.mask ? p.w0 : 0);
+        for (int c = c_lo; c < c_hi; ++c) {
+            const float4 *hw = reinterpret_cast<const float4 *>(s_w + c * F);
+            float d0 = 0.f, d1 = 0.f, d2 = 0.f, d3 = 0.f;
+#pragma unroll
+            for (int k = 0; k < F / 4; ++k) {
+                const float4 wq = hw[k];
+                d0 = fmaf(wq.x, fv[4 * k], d0); d1 = fmaf(wq.y, fv[4 * k + 1], d1);
+                d2 = fmaf(wq.z, fv[4 * k + 2], d2); d3 = fmaf(wq.w, fv[4 * k + 3], d3);
+            }
+            const float v = s_b[c] + ((d0 + d1) + (d2 + d3));
+            const bool on = h_act && v > 0.f;
+            if (p.logits && h_act) p.logits[((long long)c * p.h + y2) * p.w + x2] = v;
+            if (p.mask) s_mask[hp * heads + c] = on ? 1 : 0;
+            if (p.present) {
+                const unsigned any = __ballot_sync(0xffffffffu, on);
+                if (any && (tid & 31) == 0) s_any[c] = 1;
+            }
+        }
+    }
+    __syncthreads();
+    if (p.present)
+        for (int c = tid; c < heads; c += kBlend2Threads)
+            if (s_any[c] && __ldcg(p.present + p.ch_off + c) == 0) p.present[p.ch_off + c] = 1;
+    // ---------------- phase 3: mask bytes ----------------
+    if (p.mask) {
+        const int total = PPB * heads;
+        for (int i = tid; i < total; i += kBlend2Threads) {
+            const int pp = i / heads, c = i - pp * heads;
+            const long long b = s_base[pp];
+            if (b >= 0) p.mask[(b >> 1) + c] = s_mask[i];
+        }
+    }
+}
+
+template <int F> constexpr size_t blend2_smem_bytes(int heads, int n_img, bool ss) {
+    return (size_t)(heads * F + ((heads + 3) & ~3) + (kBlend2Threads / (F / 8)) * (F + 4) + (ss ? n_img * F * 2 : 0)) * sizeof(float) +
+           (size_t)(kBlend2Threads / (F / 8)) * sizeof(long long) + (((size_t)(kBlend2Threads / (F / 8)) * heads + 15) & ~(size_t)15) + (size_t)heads * sizeof(int);
+}
+
+}  // namespace ts2d

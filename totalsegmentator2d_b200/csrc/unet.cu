@@ -21,6 +21,7 @@
 #include "conv_halo.cuh"
 #include "conv_first_tc.cuh"
 #include "unet_kernels.cuh"
+#include "blend.cuh"
 
 namespace ts2d {
 
@@ -1064,8 +1065,44 @@ static int launch_blend(const BlendParams &p, const int *tile_yx_host, int F, cu
     TS2D_LAUNCH_CHECK();
     return TS2D_OK;
 }
+// 16-bit features: blend_head_v2_kernel (blend.cuh).  The grid covers the whole output image when a mask is written.
+template <typename T, int F, int CAP>
+static int launch_blend2_inst(const BlendParams &p, const int *tile_yx_host, int H0, cudaStream_t st) {
+    constexpr int PPB = kBlend2Threads / (F / 8);
+    const int n_img = p.T * p.M;
+    bool ss_smem = p.feat_ss != nullptr;
+    size_t smem = blend2_smem_bytes<F>(p.heads, n_img, ss_smem);
+    if (smem > 200 * 1024) { ss_smem = false; smem = blend2_smem_bytes<F>(p.heads, n_img, false); }
+    static size_t attr_smem = 48 * 1024;
+    if (smem > attr_smem) {
+        TS2D_CHECK_CUDA(cudaFuncSetAttribute(blend_head_v2_kernel<T, F, CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr_smem = 200 * 1024;
+    }
+    const int full_h = p.mask ? H0 : p.h, full_w = p.mask ? p.W0 : p.w;
+    const long long npix = (long long)full_h * full_w;
+    TileListT<CAP> tl;
+    fill_tile_list(tl, tile_yx_host, p.T);
+    blend_head_v2_kernel<T, F, CAP><<<(unsigned)ceil_div(npix, PPB), kBlend2Threads, smem, st>>>(p, tl, full_h, full_w, ss_smem ? 1 : 0);
+    TS2D_LAUNCH_CHECK();
+    return TS2D_OK;
+}
+template <typename T, int CAP>
+static int launch_blend2(const BlendParams &p, const int *tile_yx_host, int F, int H0, cudaStream_t st) {
+    switch (F) {
+        case 8: return launch_blend2_inst<T, 8, CAP>(p, tile_yx_host, H0, st);
+        case 16: return launch_blend2_inst<T, 16, CAP>(p, tile_yx_host, H0, st);
+        case 32: return launch_blend2_inst<T, 32, CAP>(p, tile_yx_host, H0, st);
+        case 64: return launch_blend2_inst<T, 64, CAP>(p, tile_yx_host, H0, st);
+        default: set_error("ts2d_unet_blend_head: features_per_stage[0] must be 8, 16, 32 or 64 (got %d)", F); return TS2D_ERR_UNSUPPORTED;
+    }
+}
+static bool blend_v2_enabled() { return env_int("TS2D_BLEND_V2", 1) != 0; }      // read per call: the tests flip it
 template <typename T>
-static int launch_blend_any(const BlendParams &p, const int *tile_yx_host, int F, cudaStream_t st) {
+static int launch_blend_any(const BlendParams &p, const int *tile_yx_host, int F, int H0, cudaStream_t st) {
+    if constexpr (sizeof(T) == 2) {
+        if (blend_v2_enabled())
+            return p.T <= 64 ? launch_blend2<T, 64>(p, tile_yx_host, F, H0, st) : launch_blend2<T, kMaxTiles>(p, tile_yx_host, F, H0, st);
+    }
     return p.T <= 64 ? launch_blend<T, 64>(p, tile_yx_host, F, st) : launch_blend<T, kMaxTiles>(p, tile_yx_host, F, st);
 }
 
@@ -1099,9 +1136,9 @@ extern "C" int ts2d_unet_blend_head(ts2d_unet *u, const int *tile_yx_host, int T
         u->launches++;
         p.feat = lastc.out_raw; p.feat_ss = u->feat_ss; p.slope = u->plan.negative_slope;
     }
-    if (u->plan.precision == TS2D_PREC_F32) rc = launch_blend_any<float>(p, tile_yx_host, u->C[0], st);
-    else if (u->plan.precision == TS2D_PREC_BF16) rc = launch_blend_any<__nv_bfloat16>(p, tile_yx_host, u->C[0], st);
-    else rc = launch_blend_any<__half>(p, tile_yx_host, u->C[0], st);
+    if (u->plan.precision == TS2D_PREC_F32) rc = launch_blend_any<float>(p, tile_yx_host, u->C[0], H0, st);
+    else if (u->plan.precision == TS2D_PREC_BF16) rc = launch_blend_any<__nv_bfloat16>(p, tile_yx_host, u->C[0], H0, st);
+    else rc = launch_blend_any<__half>(p, tile_yx_host, u->C[0], H0, st);
     if (rc) return rc;
     u->launches++;
     return TS2D_OK;
@@ -1152,6 +1189,14 @@ extern "C" int ts2d_merge_present_order(const uint8_t *src_dev, uint8_t *dst_dev
     PermList pl;
     pl.C = C;
     return launch_permute(src_dev, dst_dev, n_pix, pl, perm_dev, st);
+}
+
+extern "C" int ts2d_unet_blend_covers_image(const ts2d_unet *u) {
+    // 1: ts2d_unet_blend_head writes this model's channel window of EVERY pixel of the H0 x W0 mask (zeros outside the crop box),
+    // so the caller does not have to clear the mask first
+    if (!u) return 0;
+    const int F = u->C.empty() ? 0 : u->C[0];
+    return (u->plan.precision != TS2D_PREC_F32 && blend_v2_enabled() && (F == 8 || F == 16 || F == 32 || F == 64)) ? 1 : 0;
 }
 
 extern "C" int ts2d_unet_resize(ts2d_unet *u, int max_batch) {

@@ -129,10 +129,10 @@ class TS2D:
         offs = self.head_offsets()
         first = imgs_dev[ids[0]]
         H, W = int(first.shape[1]), int(first.shape[2])
+        # no memset: every model writes its whole channel window, zeros outside its crop box included (ts2d_unet_blend_covers_image;
+        # the models that cannot - fp32 engines, folds, resampled export - clear their own window in predict_device)
         if mask is None:
-            mask = torch.zeros((H, W, offs[-1]), dtype=torch.uint8, device=first.device)
-        else:
-            mask.zero_()
+            mask = torch.empty((H, W, offs[-1]), dtype=torch.uint8, device=first.device)
         if present is None:
             present = torch.zeros(offs[-1], dtype=torch.uint8, device=first.device)
         else:
