@@ -237,3 +237,37 @@ def test_blend_v2_equals_v1(precision, feats, mirror, monkeypatch):
     assert torch.equal(win[11:111, 13:163][sure], ma[11:111, 13:163, 5:12][sure])
     assert torch.equal(win[11:111, 13:163], (lb > 0).permute(1, 2, 0).to(torch.uint8))
     assert torch.equal(outs["0"][2], outs["1"][2])
+
+
+@pytest.mark.parametrize("precision", ["fp16", "bf16"])
+def test_conv_tc2_two_tiles_per_weight_block(precision, monkeypatch):
+    """conv_tc2_kernel (two 128-pixel tiles share every weight block; BN = 128 double-buffered and BN = 256 single-buffered TMEM,
+    stride 1 and stride 2) against conv_tc_kernel on the same layers: the MMAs accumulate the same k-chunks in the same order, only
+    the fp32 partial sums of the InstanceNorm statistics are grouped differently, so outputs agree to one storage ulp; and against
+    the fp32 oracle layer by layer."""
+    dt = torch.bfloat16 if precision == "bf16" else torch.float16
+    outs = {}
+    layers = ["enc2.0", "enc2.1", "enc3.0", "enc3.1", "dec0.0", "dec0.1", "dec1.0"]
+    for tc2 in ("0", "1"):
+        monkeypatch.setenv("TS2D_TC2", tc2)
+        monkeypatch.setenv("TS2D_TC2_MIN_UNITS", "1")
+        monkeypatch.setenv("TS2D_CONV_HALO", "0")          # every 3x3 layer goes through conv_tc / conv_tc2
+        p, sd, spec = _make([32, 64, 128, 256], (128, 160), heads=5, precision=precision, seed=23)
+        p._ensure_batch(6)
+        x, xd = _tiles(6, 2, (128, 160), 7, dt)
+        x = xd.float().cpu().permute(0, 3, 1, 2).contiguous()
+        coll = {}
+        with torch.no_grad():
+            nnunet_net.unet_forward(x, sd, spec, collect=coll)
+        outs[tc2] = {n: p.forward_debug(xd, n, tuple(coll[n].shape[1:])).cpu() for n in layers}
+        outs[tc2]["logits"] = p.predict_tile_logits(xd).cpu()
+        if tc2 == "1":
+            errs = {n: float((outs[tc2][n] - coll[n]).abs().max()) for n in layers}
+            print(precision, "conv_tc2 vs fp32 oracle:", {k: round(v, 4) for k, v in errs.items()})
+            assert max(errs.values()) <= (0.2 if precision == "bf16" else 0.03), errs
+        p.close()
+    ulp = 2.0 ** -5 if precision == "bf16" else 2.0 ** -8            # one storage ulp for |x| in [4, 8)
+    for n in layers + ["logits"]:
+        d = (outs["0"][n] - outs["1"][n]).abs()
+        assert float(d.max()) <= 2 * ulp, (n, float(d.max()))
+        assert float((d == 0).float().mean()) >= 0.99, (n, float((d == 0).float().mean()))

@@ -18,6 +18,7 @@
 #include <vector>
 
 #include "conv_tc.cuh"
+#include "conv_tc2.cuh"
 #include "conv_halo.cuh"
 #include "conv_first_tc.cuh"
 #include "unet_kernels.cuh"
@@ -283,6 +284,45 @@ static int launch_tc(int bn, int kc, const CUtensorMap &tmA, const CUtensorMap &
     return TS2D_ERR_UNSUPPORTED;
 }
 
+template <int BN, int KC, typename DT>
+static int launch_tc2_inst(const CUtensorMap &tmA, const CUtensorMap &tmB, const ConvTcParams &p, cudaStream_t st) {
+    static bool attr_set = false;
+    constexpr int smem = tc2_smem_bytes<BN, KC>();
+    if (!attr_set) {
+        TS2D_CHECK_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<BN, KC, DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_set = true;
+    }
+    const int units = (p.tiles_n * p.tiles_h * p.tiles_w / 2) * p.n_tiles_n;
+    const int gx = std::max(1, std::min(units, kNumSMs));
+    TS2D_CHECK_CUDA(launch_pdl(conv_tc2_kernel<BN, KC, DT>, dim3(gx), dim3(kTcThreads), smem, st, tmA, tmB, p));
+    TS2D_LAUNCH_CHECK();
+    return TS2D_OK;
+}
+template <typename DT>
+static int launch_tc2(int bn, const CUtensorMap &tmA, const CUtensorMap &tmB, const ConvTcParams &p, cudaStream_t st) {
+    if (bn == 256) return launch_tc2_inst<256, 64, DT>(tmA, tmB, p, st);
+    if (bn == 128) return launch_tc2_inst<128, 64, DT>(tmA, tmB, p, st);
+    set_error("no conv_tc2_kernel instantiation for BN=%d", bn);
+    return TS2D_ERR_UNSUPPORTED;
+}
+// conv_tc2_kernel (two pixel tiles per weight block): output-channel block from a cycle model of one CTA - per k-chunk
+// max(8 MMAs, TMA rows x 1.7 cycles); the BN = 256 variant exposes its epilogue (~3 k cycles per pair).  0 = not eligible.
+static int choose_bn_tc2(int cout, long long m_tiles, int k_chunks) {
+    const int on = env_int("TS2D_TC2", 1), min_units = env_int("TS2D_TC2_MIN_UNITS", kNumSMs / 2);      // read per call: the tests flip them
+    if (!on || (m_tiles & 1)) return 0;
+    int best_bn = 0;
+    double best = 1e30;
+    for (int bn : {256, 128}) {
+        if (cout % bn) continue;
+        const long long units = (m_tiles / 2) * (cout / bn);
+        if (units < min_units) continue;
+        const double per = bn == 256 ? k_chunks * 1048.0 + 3000.0 : k_chunks * 653.0 + 600.0;
+        const double t = (double)ceil_div(units, kNumSMs) * per;
+        if (t < best) { best = t; best_bn = bn; }
+    }
+    return best_bn;
+}
+
 constexpr int kHaloSmemBudget = 225 * 1024;
 static int halo_smem_bytes(int cin, int bn, int kc, int stages) {
     const int w = ((9 * cin * bn * 2) + 1023) & ~1023;
@@ -317,8 +357,7 @@ static int launch_halo(int bn, int kc, bool fuse, const CUtensorMap &tmA, const 
 
 // picks the output-channel block and ring depth of the halo kernel, or returns false when the layer should use conv_tc_kernel
 static bool halo_config(const ConvLayer &c, int &bn, int &stages) {
-    static const int enable = getenv("TS2D_CONV_HALO") ? atoi(getenv("TS2D_CONV_HALO")) : 1;
-    static const int max_nt = getenv("TS2D_HALO_MAX_NT") ? atoi(getenv("TS2D_HALO_MAX_NT")) : 2;
+    const int enable = env_int("TS2D_CONV_HALO", 1), max_nt = env_int("TS2D_HALO_MAX_NT", 2);      // read at finalize time
     if (!enable || !c.tc || c.kh != 3 || c.kw != 3 || c.sh != 1 || c.sw != 1) return false;
     if (c.Hout < 16 || c.Wout < 8) return false;
     const double covered = (double)ceil_div(c.Wout, 8) * 8 * ceil_div(c.Hout, 16) * 16;
@@ -812,12 +851,15 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
                 bn = (fbn && c.cout % fbn == 0) ? fbn : choose_bn(c.cout, m_tiles * S, c.kh * c.kw * c.cin / 16 / S);
             }
         }
+        const int mc_on = env_int("TS2D_MC", 0);
+        int bn2 = 0;                            // > 0: conv_tc2_kernel (two pixel tiles per weight block)
+        if (ksplit == 0 && tn == 1 && c.kc == 64 && c.kh * c.kw == 9 && !mc_on) bn2 = choose_bn_tc2(c.cout, m_tiles, c.kh * c.kw * c.cin / c.kc);
+        if (bn2) bn = bn2;
         fill_tc_params(p, N, c.Hout, c.Wout, c.cout, c.cin, c.kc, bn, c.kh * c.kw, c.kw, (c.kh - 1) / 2, (c.kw - 1) / 2, s2, c.in_ps);
         p.tw = tw; p.th = th; p.tn = tn;
         p.tiles_w = ceil_div(c.Wout, tw); p.tiles_h = ceil_div(c.Hout, th); p.tiles_n = ceil_div(N, tn);
         p.out_ps = c.cout; p.out = c.out_raw; p.bias = c.b.dev; p.stats = c.stats;
         if (ksplit >= 1) { p.ksplit = ksplit; p.partial = u->partial; p.stats = nullptr; p.bias = nullptr; }
-        const int mc_on = env_int("TS2D_MC", 0);
         p.mc = (mc_on && ksplit == 0 && m_tiles % 2 == 0 && bn >= 32) ? 1 : 0;
         // descriptors depend on (input pointer, batch-dependent tile box, BN): cache by (N, bn)
         if (c.first || c.bn != bn * (p.mc ? -1 : 1) || c.enc_n != N) {
@@ -837,7 +879,8 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
             TS2D_CHECK_CUDA(cudaMemsetAsync(tc_dbg, 0, kNumSMs * 8 * sizeof(long long), st));
             p.dbg = tc_dbg;
         }
-        rc = is_bf16 ? launch_tc<__nv_bfloat16>(bn, c.kc, c.tmA, c.tmB, p, st) : launch_tc<__half>(bn, c.kc, c.tmA, c.tmB, p, st);
+        if (bn2) rc = is_bf16 ? launch_tc2<__nv_bfloat16>(bn, c.tmA, c.tmB, p, st) : launch_tc2<__half>(bn, c.tmA, c.tmB, p, st);
+        else rc = is_bf16 ? launch_tc<__nv_bfloat16>(bn, c.kc, c.tmA, c.tmB, p, st) : launch_tc<__half>(bn, c.kc, c.tmA, c.tmB, p, st);
         if (rc) return rc;
         if (tc_dbg_on) {
             // clock stamps (cycles since the CTA started): prologue, first loads issued, all loads issued, first operands landed,
