@@ -191,6 +191,19 @@ int ts2d_unet_destroy(ts2d_unet *u);
 /* global launch counter of the non-engine kernels (projection, preprocessing, tiling) */
 int64_t ts2d_launch_count(void);
 
+/* ---- PNG visuals (reference ts2d/core/util/image.py:383-481 create_visual / get_auto_window, ts2d/tool.py:272-284) ----
+ * labels: uint8 mask [H][W][C] -> label = 1 + highest-index non-zero component -> nearest-neighbour uniform resampling
+ * (output index j samples input index c_in + (j - c_out) * ratio, c = size / 2, default 0 outside) -> sitk.LabelToRGB with the
+ * colour map palette_host[n_colors][3] (label L -> entry L % n_colors, background -> black).  rgb_dev: uint8 [H2][W2][3]. */
+int ts2d_visual_labels(const uint8_t *mask_dev, int C, int H, int W, int H2, int W2, double ratio_y, double ratio_x,
+                       const uint8_t *palette_host, int n_colors, uint8_t *rgb_dev, ts2d_stream stream);
+/* intensity: float32 [H][W] -> (resample != 0: cubic B-spline uniform resampling, ITK mirror boundaries) -> window
+ * [lower, upper] (auto_lower / auto_upper: minimum / maximum of the resampled image) -> IntensityWindowing to 0..255 ->
+ * uint8 by truncation.  scratch_dev: H*W + 2 doubles; resampled_dev: H2*W2 floats; out_dev: uint8 [H2][W2]. */
+int ts2d_visual_intensity(const float *img_dev, int H, int W, int H2, int W2, double ratio_y, double ratio_x, int resample,
+                          double lower, double upper, int auto_lower, int auto_upper, double *scratch_dev,
+                          float *resampled_dev, uint8_t *out_dev, ts2d_stream stream);
+
 #ifdef __cplusplus
 }
 #endif

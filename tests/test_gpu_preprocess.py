@@ -92,3 +92,44 @@ def test_extract_tiles_matches_pad_slice_flip(hw, patch, mirror):
         for m, ax in enumerate(combos):
             ref = torch.flip(tile, ax) if ax else tile
             assert torch.equal(x[t * M + m].permute(2, 0, 1), ref[0])
+
+
+def test_visual_kernels_match_create_visual_restatement():
+    """csrc/visual.cu (label flatten + nearest-neighbour uniform resampling + LabelToRGB; cubic B-spline uniform resampling +
+    minmax window + IntensityWindowing + uint8 truncation) vs oracle/visual.py, the CPU restatement of reference
+    ts2d/core/util/image.py:383-481; through the host mirror create_visual on isotropic and anisotropic images."""
+    from oracle import visual as ovis
+    from totalsegmentator2d_b200 import ops
+    from totalsegmentator2d_b200.core.util import visual as vis
+    from totalsegmentator2d_b200.core.util.meta import set_annotation_meta
+    from totalsegmentator2d_b200.image import Image
+    rng = np.random.default_rng(11)
+    # ---- labels: 13 overlapping channels, anisotropic spacing (1.5, 0.75) -> uniform 0.75 ----
+    m = (rng.random((90, 70, 13)) > 0.8).astype(np.uint8)
+    m[:10] = 0
+    size_xy, sp_xy = (70, 90), (1.5, 0.75)
+    new_size, ratios, changed = vis.uniform_geometry(size_xy, sp_xy)
+    assert changed and new_size == [140, 90]
+    cmap = vis.to_palette({i + 1: (int(rng.integers(0, 255)), int(rng.integers(0, 255)), int(rng.integers(0, 255))) for i in range(13) if i != 4})
+    got = ops.visual_labels(torch.from_numpy(m).cuda(), (new_size[1], new_size[0]), (ratios[1], ratios[0]), np.asarray(cmap, np.uint8)).cpu().numpy()
+    want = ovis.visual_labels(m, (new_size[1], new_size[0]), (ratios[1], ratios[0]), cmap)
+    assert got.shape == (90, 140, 3) and np.array_equal(got, want)
+    seg = Image(m, sp_xy, (0.0, 0.0), None, is_vector=True)
+    set_annotation_meta(seg, names={i + 1: f"n{i}" for i in range(13)}, colors={f"n{i}": tuple(cmap[i + 1]) for i in range(13)})
+    assert np.array_equal(vis.create_visual(seg, labels=True, axis="coronal"), want)
+    # ---- intensity: anisotropic (B-spline resampling) and isotropic (window only) ----
+    a = rng.normal(100, 300, size=(60, 50)).astype(np.float32)
+    new_size, ratios, changed = vis.uniform_geometry((50, 60), (1.0, 2.5))
+    assert changed and new_size == [50, 150]
+    got = ops.visual_intensity(torch.from_numpy(a).cuda(), (150, 50), (ratios[1], ratios[0])).cpu().numpy()
+    want = ovis.visual_intensity(a, (150, 50), (ratios[1], ratios[0]))
+    d = np.abs(got.astype(int) - want.astype(int))
+    assert got.shape == (150, 50) and d.max() <= 1 and (d == 0).mean() >= 0.995, (d.max(), (d == 0).mean())     # truncation of values within 1e-9 of an integer
+    got = vis.create_visual(Image(a, (1.5, 1.5), (0.0, 0.0), None))
+    want = ovis.visual_intensity(a, a.shape, (1.0, 1.0), resample=False)
+    assert np.array_equal(got, want) and got.min() == 0 and got.max() == 255
+    got = ops.visual_intensity(torch.from_numpy(a).cuda(), a.shape, (1.0, 1.0), (-200.0, 400.0)).cpu().numpy()
+    assert np.array_equal(got, ovis.visual_intensity(a, a.shape, (1.0, 1.0), (-200.0, 400.0), resample=False))
+    # ---- a 3-D projected image container (X, 1, Z) as Result.save passes it ----
+    proj = Image(a.reshape(60, 1, 50), (1.5, 403.5, 1.5), (0, 0, 0), np.diag([-1.0, -1.0, -1.0]).reshape(-1))
+    assert np.array_equal(vis.create_visual(proj), want if False else ovis.visual_intensity(a, a.shape, (1.0, 1.0), resample=False))

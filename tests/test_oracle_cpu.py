@@ -278,3 +278,22 @@ def test_nifti_and_metaimage_readers_round_trip(tmp_path):
     vi.SetMetaData("k", "a\\nb\nc\\\\")
     nrrd.write_nrrd(vi, str(tmp_path / "m.nrrd"), False)
     assert nrrd.read_nrrd(str(tmp_path / "m.nrrd")).GetMetaData("k") == "a\\nb\nc\\\\"
+
+
+def test_visual_restatement_properties():
+    """oracle/visual.py (create_visual restatement): identity geometry is the identity, label = highest non-zero component,
+    background black, 2x finer uniform grid replicates pixels around the kept centre index, window endpoints map to 0 / 255."""
+    from oracle import visual as ovis
+    m = np.zeros((4, 6, 3), np.uint8)
+    m[1, 2, 0] = 1
+    m[1, 2, 2] = 1
+    m[3, 5, 1] = 7
+    cmap = [[255, 255, 255], [10, 20, 30], [40, 50, 60], [70, 80, 90]]
+    out = ovis.visual_labels(m, (4, 6), (1.0, 1.0), cmap)
+    assert out[1, 2].tolist() == [70, 80, 90] and out[3, 5].tolist() == [40, 50, 60] and out[0, 0].tolist() == [0, 0, 0]
+    fine = ovis.visual_labels(m, (8, 6), (0.5, 1.0), cmap)               # rows twice as fine: input index 2 stays at output index 4,
+    # output rows 1, 2 sample input indices 0.5 (rounds half up to 1) and 1.0; row 3 samples 1.5 -> 2
+    assert fine.shape == (8, 6, 3) and fine[1, 2].tolist() == [70, 80, 90] and fine[2, 2].tolist() == [70, 80, 90] and fine[3, 2].tolist() == [0, 0, 0]
+    a = np.array([[0.0, 50.0], [100.0, 25.0]], np.float32)
+    assert ovis.visual_intensity(a, a.shape, (1, 1), resample=False).tolist() == [[0, 127], [255, 63]]
+    assert np.array_equal(ovis.visual_intensity(a, a.shape, (1.0, 1.0)), ovis.visual_intensity(a, a.shape, (1, 1), resample=False))

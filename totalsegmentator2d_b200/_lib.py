@@ -77,6 +77,8 @@ _PROTOS = {
     "ts2d_unet_blend_head": (_i, [_vp, _ip, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp]),
     "ts2d_threshold_logits": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "ts2d_permute_channels": (_i, [_vp, _vp, _i64, _i, _ip, _vp]),
+    "ts2d_visual_labels": (_i, [_vp, _i, _i, _i, _i, _i, C.c_double, C.c_double, C.c_char_p, _i, _vp, _vp]),
+    "ts2d_visual_intensity": (_i, [_vp, _i, _i, _i, _i, C.c_double, C.c_double, _i, C.c_double, C.c_double, _i, _i, _vp, _vp, _vp, _vp]),
     "ts2d_merge_present_order": (_i, [_vp, _vp, _i64, _i, _vp, _ip, _i, _vp, _vp]),
     "ts2d_unet_launch_count": (_i64, [_vp]),
     "ts2d_unet_blend_covers_image": (_i, [_vp]),

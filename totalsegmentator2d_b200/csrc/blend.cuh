@@ -25,13 +25,14 @@ namespace ts2d {
 
 constexpr int kBlend2Threads = 256;
 
-template <typename T, int F, int CAP>
+template <typename T, int F, int CAP, int MM /* mirror mask: 0, 1 (flip rows), 2 (flip columns), 3 (all four variants) */>
 __global__ void __launch_bounds__(kBlend2Threads, F <= 32 ? 4 : 2) blend_head_v2_kernel(const BlendParams p, const __grid_constant__ TileListT<CAP> tl, int full_h, int full_w, int ss_smem) {
     static_assert(F % 8 == 0 && F <= 64, "blend_head_v2_kernel: F must be 8, 16, 32 or 64");
     constexpr int LPP = F / 8;                       // lanes per pixel
     constexpr int PPB = kBlend2Threads / LPP;        // pixels per block
     constexpr int G = LPP;                           // head groups in phase 2 (PPB * G == 256)
     constexpr int FS = F + 4;                        // padded feature row (floats): 16-byte aligned, conflict-free float4 reads
+    constexpr int M = MM == 3 ? 4 : (MM ? 2 : 1);    // mirror variants per tile (compile time: no branches in the tile loop)
     extern __shared__ __align__(16) float s_mem[];
     // layout: head_w [heads][F] | head_b [heads] (padded to 4) | feat [PPB][FS] | ss [T*M][F][2] (scale, shift; only when feat_ss) |
     //         pixel base offsets [PPB] (long long) | mask bytes [PPB][heads] | any flags [heads] (int)
@@ -41,7 +42,7 @@ __global__ void __launch_bounds__(kBlend2Threads, F <= 32 ? 4 : 2) blend_head_v2
     float *s_b = s_w + heads * F;
     float *s_feat = s_b + hb_pad;
     float *s_ss = s_feat + PPB * FS;
-    const int n_img = p.T * p.M;
+    const int n_img = p.T * M;
     long long *s_base = reinterpret_cast<long long *>(s_ss + ((p.feat_ss && ss_smem) ? n_img * F * 2 : 0));
     uint8_t *s_mask = reinterpret_cast<uint8_t *>(s_base + PPB);
     int *s_any = reinterpret_cast<int *>(s_mask + ((PPB * heads + 15) & ~15));
@@ -76,8 +77,10 @@ __global__ void __launch_bounds__(kBlend2Threads, F <= 32 ? 4 : 2) blend_head_v2
     for (int k = 0; k < 8; ++k) acc[k] = 0.f;
     float wsum = 0.f;
     const T *feat = reinterpret_cast<const T *>(p.feat);
-    const float inv_m = 1.0f / (float)p.M;
+    const float inv_m = 1.0f / (float)M;
     const float slope = p.slope;
+    const bool slope01 = slope >= 0.f && slope <= 1.f;          // LeakyReLU(y) == max(y, slope * y)
+    const long long img_stride = (long long)p.Ph * p.Pw * F;
     if (active) {
         for (int t = 0; t < p.T; ++t) {
             const int ly = yp - tl.yx[t][0], lx = xp - tl.yx[t][1];
@@ -85,21 +88,18 @@ __global__ void __launch_bounds__(kBlend2Threads, F <= 32 ? 4 : 2) blend_head_v2
             const float g = __ldg(p.gauss + ly * p.Pw + lx);
             wsum += g;
             const float gm = g * inv_m;
-            uint4 v[4];
+            uint4 v[M];
+            const T *tbase = feat + (long long)(t * M) * img_stride + q * 8;
+            const int fy_ = p.Ph - 1 - ly, fx_ = p.Pw - 1 - lx;
 #pragma unroll
-            for (int m = 0; m < 4; ++m) {
-                if (m < p.M) {
-                    bool fh = false, fw = false;
-                    if (p.mirror_mask == 3) { fh = (m & 1) != 0; fw = (m & 2) != 0; }
-                    else if (p.mirror_mask == 1) fh = (m == 1);
-                    else if (p.mirror_mask == 2) fw = (m == 1);
-                    const int sy = fh ? p.Ph - 1 - ly : ly, sx = fw ? p.Pw - 1 - lx : lx;
-                    v[m] = __ldg(reinterpret_cast<const uint4 *>(feat + (((long long)(t * p.M + m) * p.Ph + sy) * p.Pw + sx) * F + q * 8));
-                }
+            for (int m = 0; m < M; ++m) {
+                const bool fh = MM == 3 ? (m & 1) != 0 : (MM == 1 && m == 1);
+                const bool fw = MM == 3 ? (m & 2) != 0 : (MM == 2 && m == 1);
+                v[m] = __ldg(reinterpret_cast<const uint4 *>(tbase + m * img_stride + ((long long)(fh ? fy_ : ly) * p.Pw + (fw ? fx_ : lx)) * F));
             }
 #pragma unroll
-            for (int m = 0; m < 4; ++m) {
-                if (m < p.M) {
+            for (int m = 0; m < M; ++m) {
+                {
                     const uint32_t *w = reinterpret_cast<const uint32_t *>(&v[m]);
                     float f[8];
 #pragma unroll
@@ -107,14 +107,14 @@ __global__ void __launch_bounds__(kBlend2Threads, F <= 32 ? 4 : 2) blend_head_v2
                     if (p.feat_ss) {
                         float scv[8], shv[8];
                         if (ss_smem) {
-                            const float4 *sc = reinterpret_cast<const float4 *>(s_ss + (t * p.M + m) * 2 * F + q * 8);
-                            const float4 *sh = reinterpret_cast<const float4 *>(s_ss + (t * p.M + m) * 2 * F + F + q * 8);
+                            const float4 *sc = reinterpret_cast<const float4 *>(s_ss + (t * M + m) * 2 * F + q * 8);
+                            const float4 *sh = reinterpret_cast<const float4 *>(s_ss + (t * M + m) * 2 * F + F + q * 8);
                             const float4 a0 = sc[0], a1 = sc[1], b0 = sh[0], b1 = sh[1];
                             scv[0] = a0.x; scv[1] = a0.y; scv[2] = a0.z; scv[3] = a0.w; scv[4] = a1.x; scv[5] = a1.y; scv[6] = a1.z; scv[7] = a1.w;
                             shv[0] = b0.x; shv[1] = b0.y; shv[2] = b0.z; shv[3] = b0.w; shv[4] = b1.x; shv[5] = b1.y; shv[6] = b1.z; shv[7] = b1.w;
                         } else {
                             // too many tiles for shared memory: the pair layout {sc, sc, sh, sh} straight from global memory (L1 hits)
-                            const float4 *ss = reinterpret_cast<const float4 *>(p.feat_ss) + (long long)(t * p.M + m) * (F / 2) + q * 4;
+                            const float4 *ss = reinterpret_cast<const float4 *>(p.feat_ss) + (long long)(t * M + m) * (F / 2) + q * 4;
 #pragma unroll
                             for (int j = 0; j < 4; ++j) {
                                 const float4 c4 = __ldg(ss + j);
@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(kBlend2Threads, F <= 32 ? 4 : 2) blend_head_v2
 #pragma unroll
                         for (int k = 0; k < 8; ++k) {
                             const float yv = fmaf(f[k], scv[k], shv[k]);
-                            f[k] = yv > 0.f ? yv : yv * slope;
+                            f[k] = slope01 ? fmaxf(yv, yv * slope) : (yv > 0.f ? yv : yv * slope);
                         }
                     }
 #pragma unroll

@@ -1118,14 +1118,23 @@ static int launch_blend2_inst(const BlendParams &p, const int *tile_yx_host, int
     if (smem > 200 * 1024) { ss_smem = false; smem = blend2_smem_bytes<F>(p.heads, n_img, false); }
     static size_t attr_smem = 48 * 1024;
     if (smem > attr_smem) {
-        TS2D_CHECK_CUDA(cudaFuncSetAttribute(blend_head_v2_kernel<T, F, CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        TS2D_CHECK_CUDA(cudaFuncSetAttribute(blend_head_v2_kernel<T, F, CAP, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        TS2D_CHECK_CUDA(cudaFuncSetAttribute(blend_head_v2_kernel<T, F, CAP, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        TS2D_CHECK_CUDA(cudaFuncSetAttribute(blend_head_v2_kernel<T, F, CAP, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        TS2D_CHECK_CUDA(cudaFuncSetAttribute(blend_head_v2_kernel<T, F, CAP, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         attr_smem = 200 * 1024;
     }
     const int full_h = p.mask ? H0 : p.h, full_w = p.mask ? p.W0 : p.w;
     const long long npix = (long long)full_h * full_w;
     TileListT<CAP> tl;
     fill_tile_list(tl, tile_yx_host, p.T);
-    blend_head_v2_kernel<T, F, CAP><<<(unsigned)ceil_div(npix, PPB), kBlend2Threads, smem, st>>>(p, tl, full_h, full_w, ss_smem ? 1 : 0);
+    const unsigned grid = (unsigned)ceil_div(npix, PPB);
+    switch (p.mirror_mask) {
+        case 0: blend_head_v2_kernel<T, F, CAP, 0><<<grid, kBlend2Threads, smem, st>>>(p, tl, full_h, full_w, ss_smem ? 1 : 0); break;
+        case 1: blend_head_v2_kernel<T, F, CAP, 1><<<grid, kBlend2Threads, smem, st>>>(p, tl, full_h, full_w, ss_smem ? 1 : 0); break;
+        case 2: blend_head_v2_kernel<T, F, CAP, 2><<<grid, kBlend2Threads, smem, st>>>(p, tl, full_h, full_w, ss_smem ? 1 : 0); break;
+        default: blend_head_v2_kernel<T, F, CAP, 3><<<grid, kBlend2Threads, smem, st>>>(p, tl, full_h, full_w, ss_smem ? 1 : 0); break;
+    }
     TS2D_LAUNCH_CHECK();
     return TS2D_OK;
 }

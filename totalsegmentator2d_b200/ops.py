@@ -146,5 +146,33 @@ def merge_present_order(src: torch.Tensor, present: torch.Tensor, offsets: Seque
     return out, perm
 
 
+def visual_labels(mask: torch.Tensor, new_hw, ratio_yx, palette: np.ndarray) -> torch.Tensor:
+    """create_visual for a multi-component mask (reference ts2d/core/util/image.py:431-440): [H][W][C] uint8 -> RGB uint8 [H2][W2][3]."""
+    lib = L.load()
+    H, W, Cc = mask.shape
+    H2, W2 = int(new_hw[0]), int(new_hw[1])
+    pal = np.ascontiguousarray(np.asarray(palette, dtype=np.uint8).reshape(-1, 3))
+    out = torch.empty((H2, W2, 3), dtype=torch.uint8, device=mask.device)
+    L.check(lib.ts2d_visual_labels(_dev(mask, "mask"), Cc, H, W, H2, W2, float(ratio_yx[0]), float(ratio_yx[1]), pal.tobytes(), int(pal.shape[0]),
+                                   out.data_ptr(), L.stream_ptr()), "ts2d_visual_labels")
+    return out
+
+
+def visual_intensity(img: torch.Tensor, new_hw, ratio_yx, window=(None, None)) -> torch.Tensor:
+    """create_visual for an intensity image (reference ts2d/core/util/image.py:441-451): float32 [H][W] -> uint8 [H2][W2]."""
+    lib = L.load()
+    H, W = img.shape
+    H2, W2 = int(new_hw[0]), int(new_hw[1])
+    resample = (H2, W2) != (H, W) or not np.allclose(ratio_yx, (1.0, 1.0))
+    scratch = torch.empty(H * W + 2, dtype=torch.float64, device=img.device)
+    res = torch.empty((H2, W2), dtype=torch.float32, device=img.device)
+    out = torch.empty((H2, W2), dtype=torch.uint8, device=img.device)
+    lo, hi = window
+    L.check(lib.ts2d_visual_intensity(_dev(img, "img"), H, W, H2, W2, float(ratio_yx[0]), float(ratio_yx[1]), int(resample),
+                                      float(lo if lo is not None else 0.0), float(hi if hi is not None else 0.0), int(lo is None), int(hi is None),
+                                      scratch.data_ptr(), res.data_ptr(), out.data_ptr(), L.stream_ptr()), "ts2d_visual_intensity")
+    return out
+
+
 def torch_dtype_of(precision: int):
     return _PREC_TO_TORCH[precision]
