@@ -173,6 +173,11 @@ int ts2d_merge_present_order(const uint8_t *src_dev, uint8_t *dst_dev, int64_t n
 int ts2d_unet_resize(ts2d_unet *u, int max_batch);
 /* number of kernel launches this engine issued since creation (bench.py's gpu_launches) */
 int64_t ts2d_unet_launch_count(const ts2d_unet *u);
+/* number of conv / transposed-conv layers of a REDUCED-PRECISION tensor-core plan that run on the fp32 CUDA-core parity kernel
+ * (conv_direct_kernel) because no tcgen05 kernel takes their shape (channels not a multiple of 32, kernels other than 3x3 / 1x1,
+ * strides other than 1 / 2 per axis).  ts2d_unet_finalize logs each such layer to stderr once; 0 for every nnU-Net 2-D plan tested
+ * (reference plans come from nnunetv2ml's planner: ts2d/core/inference/nnu.py:149-166). */
+int ts2d_unet_direct_layer_count(const ts2d_unet *u);
 /* conv/transposed-conv/head FLOPs (MAC = 2) of one forward at `batch` images */
 double ts2d_unet_flops(const ts2d_unet *u, int batch);
 /* device time (ms) the conv kernels of the last forward took; needs ts2d_unet_set_profiling(u, 1) */

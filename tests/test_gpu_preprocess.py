@@ -116,7 +116,11 @@ def test_visual_kernels_match_create_visual_restatement():
     assert got.shape == (90, 140, 3) and np.array_equal(got, want)
     seg = Image(m, sp_xy, (0.0, 0.0), None, is_vector=True)
     set_annotation_meta(seg, names={i + 1: f"n{i}" for i in range(13)}, colors={f"n{i}": tuple(cmap[i + 1]) for i in range(13)})
-    assert np.array_equal(vis.create_visual(seg, labels=True, axis="coronal"), want)
+    # the palette comes back from the Segment{N}_Color metadata: "r g b" floats with 3 decimals, x 255 and TRUNCATED by to_color
+    # (reference color.py:72-85, meta.py:213-230): 37 -> "0.145" -> 36.  The expectation takes the same round trip on the host.
+    rt = {i + 1: tuple(int(float(np.format_float_positional(c / 255.0, precision=3, unique=False)) * 255) for c in cmap[i + 1]) for i in range(13)}
+    want_rt = ovis.visual_labels(m, (new_size[1], new_size[0]), (ratios[1], ratios[0]), vis.to_palette(rt))
+    assert np.array_equal(vis.create_visual(seg, labels=True, axis="coronal"), want_rt)
     # ---- intensity: anisotropic (B-spline resampling) and isotropic (window only) ----
     a = rng.normal(100, 300, size=(60, 50)).astype(np.float32)
     new_size, ratios, changed = vis.uniform_geometry((50, 60), (1.0, 2.5))

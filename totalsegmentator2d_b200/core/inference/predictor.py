@@ -205,6 +205,10 @@ class B200nnUNetPredictor:
     def launch_count(self) -> int:
         return sum(int(self._lib.ts2d_unet_launch_count(h)) for h in self._handles)
 
+    def direct_layer_count(self) -> int:
+        """layers of a reduced-precision tensor-core plan that run on the CUDA-core parity kernel (0 = every conv is on tcgen05)"""
+        return sum(int(self._lib.ts2d_unet_direct_layer_count(h)) for h in self._handles)
+
     def flops(self, batch: int) -> float:
         return float(self._lib.ts2d_unet_flops(self._handles[0], batch)) * len(self._handles)
 

@@ -7,8 +7,8 @@
 //   A  NHWC activations. One K-chunk = (filter tap, KC input channels). The 128 pixels of a tile are a
 //      (tn images) x (th rows) x (tw cols) box, so a tap is the same box shifted by (r-pad, s-pad): ONE 4-D TMA
 //      box load per K-chunk; TMA zero-fills out-of-bounds coordinates, which *is* the conv zero padding.
-//      Stride-2 convs use a 5-D "parity" view of the same buffer (w = 2*w2 + px folded into the channel axis,
-//      h = 2*h2 + py as its own axis), so every tap is again a dense box.  The box lands in shared memory as
+//      Strided convs use a 5-D "parity" view of the same buffer (w = 2*w2 + px folded into the channel axis,
+//      h = 2*h2 + py as its own axis; each axis independently, so (2,1) / (1,2) strides work too), so every tap is again a dense box.  The box lands in shared memory as
 //      128 rows x KC channels with the 128-byte (KC=64) or 64-byte (KC=32) swizzle = the canonical K-major
 //      UMMA operand layout.
 //   B  weights repacked [tap][Cout][Cin] (K-major), 3-D TMA box (KC, BN, 1).
@@ -34,7 +34,7 @@ struct ConvTcParams {
     int cin_chunks;              // Cin / KC
     int taps, kw;                // taps = kh*kw (1 for 1x1 / transposed conv slices)
     int pad_h, pad_w;
-    int stride2;                 // 0: stride 1 (4-D map), 1: stride (2,2) (5-D parity map)
+    int stride2;                 // 0: stride 1 (4-D map); else the 5-D parity map, bit 0 = stride 2 along w, bit 1 = stride 2 along h
     int in_ps;                   // input pixel stride in elements (parity view: px * in_ps selects the odd column)
     int tw, th, tn;              // tile box: tw*th*tn == 128
     int tiles_w, tiles_h, tiles_n;
@@ -70,7 +70,21 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+// `make SPIN_LIMIT=n` (-DTS2D_MBAR_SPIN_LIMIT=n): a wait that fails n try_wait rounds prints the barrier and traps, so a wrong
+// expect-tx byte count or a lost arrival is an error code (cudaErrorLaunchFailure) instead of a hung GPU.  Off in the product build.
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+#ifdef TS2D_MBAR_SPIN_LIMIT
+    for (long long spin = 0;; ++spin) {
+        uint32_t ok;
+        asm volatile("{\n.reg .pred P1;\nmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\nselp.u32 %0, 1, 0, P1;\n}"
+                     : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+        if (ok) return;
+        if (spin > (long long)(TS2D_MBAR_SPIN_LIMIT)) {
+            printf("ts2d: mbarrier wait timed out: block %d thread %d barrier smem+%u parity %u\n", (int)blockIdx.x, (int)threadIdx.x, smem_u32(bar), parity);
+            __trap();
+        }
+    }
+#endif
     asm volatile(
         "{\n"
         ".reg .pred P1;\n"
@@ -374,8 +388,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     } else {
                         // input row 2*oy + r - pad = 2*h2 + py ; input col 2*ox + s - pad = 2*w2 + px
                         const int dr = r - p.pad_h, ds = s - p.pad_w;
-                        const int py = dr & 1, px = ds & 1;
-                        const int hoff = (dr - py) / 2, woff = (ds - px) / 2;
+                        const int py = (p.stride2 & 2) ? (dr & 1) : 0, px = (p.stride2 & 1) ? (ds & 1) : 0;
+                        const int hoff = (p.stride2 & 2) ? (dr - py) / 2 : dr, woff = (p.stride2 & 1) ? (ds - px) / 2 : ds;
                         tma_load_5d(sa, &tmA, &full_bar[stage], px * p.in_ps + cc * KC, x0 + woff, py, y0 + hoff, n0);
                     }
                     if (p.mc) tma_load_3d_mc(sb + rank * (BN / 2 * KC * 2), &tmB, &full_bar[stage], cc * KC, nt * BN + (int)rank * (BN / 2), tap, (uint16_t)3);

@@ -94,8 +94,8 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                             tma_load_4d(sa + t * kABytes, &tmA, &full_bar[stage], cc * KC, x0[t] + s - p.pad_w, y0[t] + r - p.pad_h, n0[t]);
                         } else {
                             const int dr = r - p.pad_h, ds = s - p.pad_w;
-                            const int py = dr & 1, px = ds & 1;
-                            const int hoff = (dr - py) / 2, woff = (ds - px) / 2;
+                            const int py = (p.stride2 & 2) ? (dr & 1) : 0, px = (p.stride2 & 1) ? (ds & 1) : 0;
+                            const int hoff = (p.stride2 & 2) ? (dr - py) / 2 : dr, woff = (p.stride2 & 1) ? (ds - px) / 2 : ds;
                             tma_load_5d(sa + t * kABytes, &tmA, &full_bar[stage], px * p.in_ps + cc * KC, x0[t] + woff, py, y0[t] + hoff, n0[t]);
                         }
                     }

@@ -116,6 +116,7 @@ struct ts2d_unet {
     void *features = nullptr;     // last decoder output [N][P][P][C0]
     int last_batch = 0;
     long long launches = 0;
+    int direct_layers = 0;        // layers of a reduced-precision tensor-core plan that fell to conv_direct_kernel (logged at finalize)
     bool profiling = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
     int prof_used = 0;
@@ -214,8 +215,9 @@ static int encode_map(CUtensorMap *tm, void *base, int rank, const cuuint64_t *d
     return TS2D_OK;
 }
 
-// activation map for a conv input: stride 1 -> (C, W, H, N); stride 2 -> parity view (px*ps + C, W/2, 2, H/2, N)
-static int encode_act_map(CUtensorMap *tm, const void *base, long long ps, int Cin, int Hin, int Win, int Nmax, bool stride2, int kc, int tw, int th,
+// activation map for a conv input: stride 1 -> (C, W, H, N); strided -> parity view (px*ps + C, W/sw, sh, H/sh, N) with
+// w = sw*w2 + px (px folded into the channel axis when sw == 2) and h = sh*h2 + py; stride2 = (sw == 2) | (sh == 2) << 1
+static int encode_act_map(CUtensorMap *tm, const void *base, long long ps, int Cin, int Hin, int Win, int Nmax, int stride2, int kc, int tw, int th,
                           int tn, size_t es, bool is_bf16) {
     // a box that takes only part of every pixel (half of a concat buffer, or every other pixel of the parity view) must not be
     // promoted to 256-byte L2 requests: the other half is fetched from DRAM and never used (TS2D_L2PROMO_SUB, measured on enc1.0)
@@ -227,8 +229,9 @@ static int encode_act_map(CUtensorMap *tm, const void *base, long long ps, int C
         cuuint32_t box[4] = {(cuuint32_t)kc, (cuuint32_t)tw, (cuuint32_t)th, (cuuint32_t)tn};
         return encode_map(tm, const_cast<void *>(base), 4, dims, str, box, kc, es, is_bf16, promo);
     }
-    cuuint64_t dims[5] = {(cuuint64_t)(ps + Cin), (cuuint64_t)(Win / 2), 2, (cuuint64_t)(Hin / 2), (cuuint64_t)Nmax};
-    cuuint64_t str[4] = {(cuuint64_t)(2 * ps * es), (cuuint64_t)(ps * es * Win), (cuuint64_t)(2 * ps * es * Win), (cuuint64_t)(ps * es * Win * Hin)};
+    const int sw = (stride2 & 1) ? 2 : 1, sh = (stride2 & 2) ? 2 : 1;
+    cuuint64_t dims[5] = {(cuuint64_t)(sw == 2 ? ps + Cin : Cin), (cuuint64_t)(Win / sw), (cuuint64_t)sh, (cuuint64_t)(Hin / sh), (cuuint64_t)Nmax};
+    cuuint64_t str[4] = {(cuuint64_t)(sw * ps * es), (cuuint64_t)(ps * es * Win), (cuuint64_t)(sh * ps * es * Win), (cuuint64_t)(ps * es * Win * Hin)};
     cuuint32_t box[5] = {(cuuint32_t)kc, (cuuint32_t)tw, 1, (cuuint32_t)th, (cuuint32_t)tn};
     return encode_map(tm, const_cast<void *>(base), 5, dims, str, box, kc, es, is_bf16, promo);
 }
@@ -486,18 +489,17 @@ static bool tc_eligible(const ts2d_unet_plan &pl, int cin, int cout, int kh, int
     if (!pl.use_tensor_cores || pl.precision == TS2D_PREC_F32) return false;
     if (cin % 32 || cout % 32 || in_ps % 8) return false;
     if (!((kh == 3 && kw == 3) || (kh == 1 && kw == 1))) return false;
-    if (sh == 1 && sw == 1) return true;
-    if (sh == 2 && sw == 2 && Hin % 2 == 0 && Win % 2 == 0) return true;
-    return false;
+    // strides 1 / 2 per axis (anisotropic plans included); ts2d_unet_create guarantees Hin % sh == 0 and Win % sw == 0
+    return (sh == 1 || sh == 2) && (sw == 1 || sw == 2) && Hin % sh == 0 && Win % sw == 0;
 }
 
 static void fill_tc_params(ConvTcParams &p, int N, int Hout, int Wout, int cout, int cin, int kc, int bn, int taps, int kw, int pad_h, int pad_w,
-                           bool stride2, long long in_ps) {
+                           int stride2, long long in_ps) {
     memset(&p, 0, sizeof(p));
     p.N = N; p.Hout = Hout; p.Wout = Wout; p.Cout = cout;
     p.cin_chunks = cin / kc;
     p.taps = taps; p.kw = kw; p.pad_h = pad_h; p.pad_w = pad_w;
-    p.stride2 = stride2 ? 1 : 0;
+    p.stride2 = stride2;
     p.in_ps = (int)in_ps;
     p.n_tiles_n = cout / bn;
     p.tap_cout = cout;
@@ -750,6 +752,22 @@ extern "C" int ts2d_unet_finalize(ts2d_unet *u) {
         up.enc_n = 0;
     }
     if ((rc = upload(u->head_w)) || (rc = upload(u->head_b))) return rc;
+    // a reduced-precision tensor-core plan must not fall to the CUDA-core parity kernel silently (it is 10-50x slower)
+    u->direct_layers = 0;
+    if (pl.use_tensor_cores && pl.precision != TS2D_PREC_F32) {
+        for (auto &c : u->convs)
+            if (!c.tc && !c.first_tc && !c.first_fast) {
+                ++u->direct_layers;
+                fprintf(stderr, "[ts2d] warning: %s (Cin %d, Cout %d, kernel %dx%d, stride %dx%d, input %dx%d) has no tcgen05 kernel: it runs on conv_direct_kernel\n",
+                        c.name.c_str(), c.cin, c.cout, c.kh, c.kw, c.sh, c.sw, c.Hin, c.Win);
+            }
+        for (auto &up : u->ups)
+            if (!up.tc) {
+                ++u->direct_layers;
+                fprintf(stderr, "[ts2d] warning: %s (transposed conv, Cin %d, Cout %d, stride %dx%d) has no tcgen05 kernel: it runs on conv_direct_kernel\n",
+                        up.name.c_str(), up.cin, up.cout, up.sh, up.sw);
+            }
+    }
     u->finalized = true;
     u->last_batch = 0;
     return TS2D_OK;
@@ -757,6 +775,7 @@ extern "C" int ts2d_unet_finalize(ts2d_unet *u) {
 
 extern "C" size_t ts2d_unet_workspace_bytes(const ts2d_unet *u) { return u ? u->arena_bytes : 0; }
 extern "C" int64_t ts2d_unet_launch_count(const ts2d_unet *u) { return u ? u->launches : 0; }
+extern "C" int ts2d_unet_direct_layer_count(const ts2d_unet *u) { return u ? u->direct_layers : 0; }
 
 extern "C" double ts2d_unet_flops(const ts2d_unet *u, int batch) {
     if (!u) return 0.0;
@@ -827,7 +846,7 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
             p.in_eps = pl.eps; p.in_slope = pl.negative_slope;
         }
         if (c.first || !c.halo_maps) {
-            if ((rc = encode_act_map(&c.tmA, c.in, c.in_ps, c.cin, c.Hin, c.Win, pl.max_batch, false, c.kc, kHaloW, kHaloH, 1, es, is_bf16))) return rc;
+            if ((rc = encode_act_map(&c.tmA, c.in, c.in_ps, c.cin, c.Hin, c.Win, pl.max_batch, 0, c.kc, kHaloW, kHaloH, 1, es, is_bf16))) return rc;
             if ((rc = encode_w_map(&c.tmB, c.w_tc, c.cin, c.cout, 9, c.kc, c.halo_bn, es, is_bf16))) return rc;
             c.halo_maps = true;
         }
@@ -837,7 +856,7 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
         if (rc) return rc;
     } else if (c.tc) {
         ConvTcParams p;
-        const bool s2 = c.sh == 2;
+        const int s2 = (c.sw == 2 ? 1 : 0) | (c.sh == 2 ? 2 : 0);       // parity view per strided axis
         int tw, th, tn;
         choose_tile(c.Hout, c.Wout, N, tw, th, tn);
         const long long m_tiles = (long long)ceil_div(c.Wout, tw) * ceil_div(c.Hout, th) * ceil_div(N, tn);
@@ -978,7 +997,7 @@ static int run_up(ts2d_unet *u, UpLayer &up, int N, cudaStream_t st) {
         // GEMM N axis = (tap, Cout): all taps of a pixel in one pass over A; the epilogue scatters column block (tap, c0)
         const int n_total = taps * up.cout;
         const int bn = choose_bn(n_total, m_tiles, up.cin / 16);
-        fill_tc_params(p, N, up.Hin, up.Win, n_total, up.cin, up.kc, bn, 1, 1, 0, 0, false, up.cin);
+        fill_tc_params(p, N, up.Hin, up.Win, n_total, up.cin, up.kc, bn, 1, 1, 0, 0, 0, up.cin);
         p.tap_cout = up.cout;
         p.tw = tw; p.th = th; p.tn = tn;
         p.tiles_w = ceil_div(up.Win, tw); p.tiles_h = ceil_div(up.Hin, th); p.tiles_n = ceil_div(N, tn);
@@ -987,7 +1006,7 @@ static int run_up(ts2d_unet *u, UpLayer &up, int N, cudaStream_t st) {
         const int mc_on = env_int("TS2D_MC", 0);
         p.mc = (mc_on && m_tiles % 2 == 0) ? 1 : 0;
         if (up.bn != bn * (p.mc ? -1 : 1) || up.enc_n != N) {
-            if ((rc = encode_act_map(&up.tmA, up.in, up.cin, up.cin, up.Hin, up.Win, pl.max_batch, false, up.kc, tw, th, tn, es, is_bf16))) return rc;
+            if ((rc = encode_act_map(&up.tmA, up.in, up.cin, up.cin, up.Hin, up.Win, pl.max_batch, 0, up.kc, tw, th, tn, es, is_bf16))) return rc;
             if ((rc = encode_w_map(&up.tmB, up.w_tc, up.cin, n_total, 1, up.kc, p.mc ? bn / 2 : bn, es, is_bf16))) return rc;      // [tap][Cout][Cin] viewed as [taps*Cout][Cin]
             up.bn = bn * (p.mc ? -1 : 1);
             up.enc_n = N;
