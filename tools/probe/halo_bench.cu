@@ -7,6 +7,7 @@
 #include <cstdlib>
 #include <vector>
 #include <algorithm>
+#define TS2D_HALO_PROBE 1
 #include "../../totalsegmentator2d_b200/csrc/conv_halo.cuh"
 using namespace ts2d;
 
@@ -76,7 +77,7 @@ static float run(const Layer &L, int stages, int dbg, bool timing, int reps, __n
     for (int r = 0; r < reps + 2; ++r) {
         CK(cudaMemsetAsync(stats, 0, (size_t)L.N * L.Cout * 2 * sizeof(double)));
         CK(cudaEventRecord(e0));
-        conv_halo_kernel<BN, KC, __nv_bfloat16, FUSE><<<dim3(gx, nt), kHaloThreads, smem>>>(tmA, tmB, p);
+        conv_halo_kernel<BN, KC, __nv_bfloat16, FUSE><<<dim3(gx, nt), halo_threads<FUSE>(), smem>>>(tmA, tmB, p);
         CK(cudaEventRecord(e1));
         CK(cudaEventSynchronize(e1));
         CK(cudaGetLastError());
@@ -126,7 +127,7 @@ int main(int argc, char **argv) {
         CK(cudaMalloc(&g_in_stats, h.size() * 8));
         CK(cudaMemcpy(g_in_stats, h.data(), h.size() * 8, cudaMemcpyHostToDevice));
     }
-    const int dbgs[] = {0, 16, 16 + 32, 16 + 64, 16 + 32 + 64, 16 + 3};   // bit 16 (harness only): FUSE variant
+    const int dbgs[] = {0, 16, 16 + 64, 16 + 128, 16 + 256};   // 128: transform without shared-memory loads / stores, 256: without arithmetic   // bit 16 (harness only): FUSE variant
     printf("dbg bits: 1 no stats, 2 no stores, 4 tap 0 only, 8 all halos = tile 0 (L2 hits), 16 FUSE (deferred InstanceNorm on the halo)\n");
     for (const Layer &L : layers) {
         const int kc = L.Cin % 64 == 0 ? 64 : 32;

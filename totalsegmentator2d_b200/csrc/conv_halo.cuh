@@ -25,13 +25,17 @@
 // outside the image stay zeros = the conv padding of the normalised tensor), so the normalised tensor is never
 // written to or read from HBM.  Same arithmetic as norm_act_kernel: the two paths are bit-identical.
 //
-// Warp roles (384 threads): warp 0 TMA producer, warp 1 TMEM alloc + MMA issuer (whole warp convergent, one elected
-// lane issues), warps 2-3 idle, warps 4-11 = 8 WORKER warps.  A worker alternates between two duties, both of which
-// are latency bound when left to one warp per scheduler:
-//   transform (FUSE)  all 256 worker threads rewrite the halo of tile j (16-byte chunks, loads batched before math);
-//   epilogue          TMEM -> +bias -> round -> per-thread InstanceNorm partial sums -> 32-byte global stores, for
-//                     tile j - kLag (statistics from the fp32 values, FADD2 / FFMA2: see epi_chunk).  BN == 32: the two worker warpgroups alternate tiles (group g owns TMEM buffer
-//                     g); BN == 64: both work on every tile, one half of the columns each.
+// Warp roles (384 threads; see kHaloWarpMma for why in this order): warps 0-7 = 8 EPILOGUE warps, warps 8-9 = halo TRANSFORM warps
+// (FUSE only, idle otherwise), warp 10 TMA producer, warp 11 TMEM alloc + MMA issuer (whole warp convergent, one elected lane issues):
+//   transform (FUSE)  64 threads rewrite every halo stage in place between the TMA arrival (full) and the MMAs (ready): a thread owns
+//                     one 16-byte channel block (its 8 scale / shift pairs live in registers) and walks the halo pixels, loads
+//                     batched before the math; fp32x2 FMA, leaky = max(y, slope*y).  The roles are decoupled: the first version ran
+//                     the transform on the epilogue warps (transform of tile j, then epilogue of tile j-2) and the MMA warp waited
+//                     for TMEM 43% of the time (profiles/r02b_halo_bench_fuse.txt: 2396 cycles per tile against 1025 unfused,
+//                     1790 with an EMPTY transform).
+//   epilogue          TMEM -> +bias -> round -> per-thread InstanceNorm partial sums -> 32-byte global stores (statistics from the
+//                     fp32 values, FADD2 / FFMA2: see epi_chunk).  BN == 32: the two warpgroups alternate tiles (group g owns
+//                     TMEM buffer g); BN == 64: both work on every tile, one half of the columns each.
 #pragma once
 #include "conv_tc.cuh"
 
@@ -62,17 +66,39 @@ struct ConvHaloParams {
 };
 
 constexpr int kHaloW = 10, kHaloH = 18, kHaloPix = kHaloW * kHaloH;
-constexpr int kHaloThreads = 384;
-constexpr int kHaloWorkers = 256;
+constexpr int kHaloWorkers = 256;           // epilogue threads: warps 0-7
+// Warp roles by warp id.  The latency-critical single warps sit on top (the issue arbiter of an SM sub-partition prefers the highest
+// warp id among its eligible warps), the eight epilogue warps, which mostly wait, are warps 0-7 (TMEM lane quarter = warp % 4 as the
+// hardware requires).  Plain kernel: 384 threads = epilogue 0-7, (8-9 idle), TMA producer 10, MMA issuer 11.  FUSE kernel: 512 threads =
+// ONE epilogue warpgroup 0-3, EIGHT transform warps 4-11, (12-13 idle), TMA producer 14, MMA issuer 15.  Why eight: one warp sustains only ~0.4 instructions per cycle
+// on this dependent fp32x2 code (tools/probe/xform_rate.cu: 107 cycles per 40-instruction step, alone on its SM sub-partition and
+// whether or not other warps spin), a 128-byte-per-pixel stage is 45 such steps = 4800 warp-cycles, and the MMAs of a tile need
+// 1000 - 2000 cycles.  Registers: 512 threads start at 128 each; the epilogue warpgroup raises its share to 168 / 216 (setmaxnreg), the
+// transform warpgroups drop to 96, the TMA / MMA warpgroup to 64.
+template <bool FUSE> constexpr int halo_threads() { return FUSE ? 512 : 384; }
+template <bool FUSE> constexpr int halo_warp_tma() { return halo_threads<FUSE>() / 32 - 2; }
+template <bool FUSE> constexpr int halo_warp_mma() { return halo_threads<FUSE>() / 32 - 1; }
+constexpr int kHaloXformThreads = 256;      // FUSE: warps 4-11 (two warpgroups)
 
 template <int KC> constexpr int halo_stage_bytes() { return ((kHaloPix * KC * 2 + 1023) / 1024) * 1024; }
-// bytes after the halo ring: barriers (512) + bias [64] + scale/shift table [2][Cin <= 256]
-constexpr int kHaloTailBytes = 512 + 64 * 4 + 2 * 256 * 4;
+// bytes after the halo ring: barriers (512) + bias [64] + scale/shift table [2][Cin <= kHaloMaxCin]
+constexpr int kHaloMaxCin = 256;
+constexpr int kHaloTailBytes = 512 + 64 * 4 + 2 * kHaloMaxCin * 4;
 
+// explicit shared-space 16-byte accesses: the halo ring is addressed through a pointer whose alignment arithmetic hides the address
+// space from the compiler, and GENERIC LD.E.128 / ST.E.128 on shared memory made the transform ~3x slower than LDS / STS
+__device__ __forceinline__ uint4 lds128(uint32_t saddr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(saddr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts128(uint32_t saddr, const uint4 &v) {
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(saddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
 __device__ __forceinline__ void named_bar_sync(int id, int threads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory"); }
 
 template <int BN, int KC, typename DT, bool FUSE>
-__global__ void __launch_bounds__(kHaloThreads, 1)
+__global__ void __launch_bounds__(halo_threads<FUSE>(), 1)
 conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const ConvHaloParams p) {
     static_assert(BN == 32 || BN == 64, "conv_halo_kernel: BN must be 32 or 64");
     constexpr int kRowB = KC * 2;                      // bytes per pixel row of the operand
@@ -81,8 +107,9 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     constexpr int kWBlock = BN * kRowB;                // one (cin chunk, tap) weight block
     constexpr int kTmemCols = TcCfg<BN>::kTmemCols;
     constexpr int kMaxStages = 8;
+    constexpr int kHaloWarpTma = halo_warp_tma<FUSE>(), kHaloWarpMma = halo_warp_mma<FUSE>();
+    constexpr int kEpiWarps = FUSE ? 4 : 8;
     constexpr bool kSplit = BN > 32;                   // both worker groups on every tile (column halves) vs alternating tiles
-    constexpr int kLag = FUSE ? 2 : 0;                 // a worker runs the epilogue of tile j - kLag after the transform of tile j
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -97,32 +124,32 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     uint64_t *w_bar = tmem_empty + 2;
     uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(w_bar + 1);
     float *s_bias = reinterpret_cast<float *>(reinterpret_cast<uint8_t *>(full_bar) + 512);     // [64]
-    float *s_ss = s_bias + 64;                                                                   // [2][Cin]: scale, shift of the current image
+    float *s_ss = s_bias + 64;                                                                   // [2][kHaloMaxCin]: scale, shift of the transform warps' current image
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int nt = blockIdx.y;                         // output-channel block of this CTA
 
-    if (warp == 0 && lane == 0) {
+    if (warp == kHaloWarpTma && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
-        for (int s = 0; s < p.n_stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); mbar_init(&ready_bar[s], kHaloWorkers); }
-        for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], kSplit ? 256 : 128); }
+        for (int s = 0; s < p.n_stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); mbar_init(&ready_bar[s], kHaloXformThreads / 32); }      // one elected arrival per transform warp
+        for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], (!FUSE && kSplit) ? 256 : 128); }
         mbar_init(w_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 1) {
+    if (warp == kHaloWarpMma) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr)), "n"(kTmemCols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
-    if (warp >= 4)
-        for (int i = threadIdx.x - 128; i < BN; i += kHaloWorkers) s_bias[i] = p.bias ? p.bias[blockIdx.y * BN + i] : 0.f;
+    if (warp < 4)
+        for (int i = threadIdx.x; i < BN; i += 128) s_bias[i] = p.bias ? p.bias[blockIdx.y * BN + i] : 0.f;
     tcgen05_fence_before();
     __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
     griddep_launch_dependents();
-    if (!(warp == 0 && lane == 0)) griddep_wait();      // (the producer thread first issues the weight loads: constants, see below)
+    if (!(warp == kHaloWarpTma && lane == 0)) griddep_wait();      // (the producer thread first issues the weight loads: constants, see below)
 
     const int tiles_per_img = p.tiles_x * p.tiles_y;
     const int total_tiles = tiles_per_img * p.N;
@@ -133,203 +160,52 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int t_begin = (int)((long long)total_tiles * blockIdx.x / gridDim.x);
     const int t_end = (int)((long long)total_tiles * (blockIdx.x + 1) / gridDim.x);
 
-    if (warp == 0) {
-        // ===================== TMA producer =====================
-        if (lane == 0) {
-            mbar_expect_tx(w_bar, (uint32_t)w_bytes);
-            for (int cc = 0; cc < p.cin_chunks; ++cc)
-                for (int tap = 0; tap < 9; ++tap)
-                    tma_load_3d(smem_w + (cc * 9 + tap) * kWBlock, &tmB, w_bar, cc * KC, nt * BN, tap);
-            griddep_wait();                             // the resident weights stream in while the previous launch drains
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int tile = t_begin; tile < t_end; ++tile) {
-                const int tx = tile % p.tiles_x, ty = (tile / p.tiles_x) % p.tiles_y, n = tile / tiles_per_img + p.n_base;
-                for (int cc = 0; cc < p.cin_chunks; ++cc) {
-                    mbar_wait(&empty_bar[stage], phase ^ 1);
-                    mbar_expect_tx(&full_bar[stage], kHaloBytes);
-                    if (p.dbg & 8) tma_load_4d(smem_a + stage * kStageBytes, &tmA, &full_bar[stage], cc * KC, -1, -1, p.n_base);
-                    else tma_load_4d(smem_a + stage * kStageBytes, &tmA, &full_bar[stage], cc * KC, tx * 8 - 1, ty * 16 - 1, n);
-                    if (++stage == p.n_stages) { stage = 0; phase ^= 1; }
-                }
-            }
+    if (warp < kEpiWarps) {
+        // ===================== epilogue warps =====================
+        // plain kernel: warps 0-7 = two warpgroups; BN == 32: the groups alternate tiles (group g owns TMEM buffer g), BN == 64: both work on
+        // every tile, one 32-column half each.  FUSE kernel: warps 0-3 = ONE warpgroup takes every tile and all BN / 32 chunks (it has the
+        // time: the MMAs of a tile take 1000 - 4000 cycles, a chunk ~350), which leaves eight warps to the transform.
+        if constexpr (FUSE) {
+            if constexpr (BN == 64) asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");      // 2 x 64 statistics accumulators live in registers
+            else asm volatile("setmaxnreg.inc.sync.aligned.u32 168;");
         }
-    } else if (warp == 1) {
-        // ===================== MMA issuer (whole warp convergent, one elected lane issues; see conv_tc.cuh) =====================
-        const uint32_t leader = elect_one();
-        const uint32_t idesc = make_idesc<DT>(BN);
-        constexpr uint32_t a_hi = desc_hi<KC>(kHaloW * kRowB);        // 8-row groups of the A view are one halo row (10 pixels) apart
-        constexpr uint32_t b_hi = desc_hi<KC>(KC == 64 ? 1024 : 512);
-        const uint32_t w_lo = desc_lo<KC>(smem_u32(smem_w));
-        const uint32_t a0_lo = desc_lo<KC>(smem_u32(smem_a));
-        mbar_wait(w_bar, 0);
-        tcgen05_fence_after();
-        int stage = 0;
-        uint32_t phase = 0;
-        int it = 0;
-        long long t_start = 0, w_halo = 0, w_tmem = 0;
-        if (p.dbg_out) t_start = clock64();
-        for (int tile = t_begin; tile < t_end; ++tile, ++it) {
-            const int buf = it & 1;
-            const uint32_t use = (uint32_t)(it >> 1);
-            long long t0 = p.dbg_out ? clock64() : 0;
-            mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);
-            if (p.dbg_out) w_tmem += clock64() - t0;
-            tcgen05_fence_after();
-            const uint32_t d_tmem = tmem_base + (uint32_t)(buf * BN);
-            for (int cc = 0; cc < p.cin_chunks; ++cc) {
-                t0 = p.dbg_out ? clock64() : 0;
-                mbar_wait(FUSE ? &ready_bar[stage] : &full_bar[stage], phase);
-                if (p.dbg_out) w_halo += clock64() - t0;
-                tcgen05_fence_after();
-                const uint32_t a_lo = a0_lo + (uint32_t)(stage * (kStageBytes >> 4));
-                const uint32_t b_lo = w_lo + (uint32_t)(cc * 9 * (kWBlock >> 4));
-#pragma unroll
-                for (int tap = 0; tap < 9; ++tap) {
-                    if ((p.dbg & 4) && tap) continue;
-                    const int r = tap / 3, s = tap % 3;
-#pragma unroll
-                    for (int k = 0; k < KC / 16; ++k)
-                        tcgen05_mma_f16_lohi(leader, d_tmem, a_lo + (uint32_t)((((r * kHaloW + s) * kRowB) >> 4) + k * 2), a_hi,
-                                             b_lo + (uint32_t)(((tap * kWBlock) >> 4) + k * 2), b_hi, idesc, (tap | k) ? 1u : (uint32_t)(cc != 0));
-                }
-                tcgen05_commit_pred(leader, &empty_bar[stage]);
-                if (++stage == p.n_stages) { stage = 0; phase ^= 1; }
-            }
-            tcgen05_commit_pred(leader, &tmem_full[buf]);
-        }
-        if (p.dbg_out && leader) {
-            unsigned long long *o = p.dbg_out + (size_t)(blockIdx.y * gridDim.x + blockIdx.x) * 8;
-            o[0] = (unsigned long long)(clock64() - t_start); o[1] = (unsigned long long)w_halo; o[2] = (unsigned long long)w_tmem;
-        }
-    } else if (warp >= 4) {
-        // ===================== workers (warps 4..11): halo transform of tile j, then epilogue of tile j - kLag =====================
-        const int wt = threadIdx.x - 128;       // 0..255
-        const int grp = wt >> 7;                // worker warpgroup
+        const int wt = threadIdx.x;             // 0..255 (FUSE: 0..127)
+        const int grp = wt >> 7;                // epilogue warpgroup
         const int q = warp & 3;                 // TMEM lane quarter this warp may access
         const int row = q * 32 + lane;
         const int ix = row & 7, iy = row >> 3;
-        const int col0 = kSplit ? grp * 32 : 0;
+        constexpr int kChunks = FUSE ? BN / 32 : 1;                   // 32-column chunks per thread and tile
+        constexpr bool kAltTiles = !FUSE && !kSplit;                  // the two groups alternate tiles
+        const int col0 = (!FUSE && kSplit) ? grp * 32 : 0;
         DT *out = reinterpret_cast<DT *>(p.out);
         const bool do_stats = p.stats != nullptr && !(p.dbg & 1);
         // InstanceNorm statistics: every thread keeps running sums of ITS pixel row for its 32 channels across the tiles of
         // one image (no cross-lane traffic per tile); the 32-lane transpose-reduction and the double atomics happen only
         // when the image changes (<= 3 flushes per CTA with the contiguous partition).
-        uint64_t tacc1[16], tacc2[16];
+        uint64_t tacc1[kChunks][16], tacc2[kChunks][16];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) { tacc1[i] = 0ull; tacc2[i] = 0ull; }
+        for (int c = 0; c < kChunks; ++c)
+#pragma unroll
+            for (int i = 0; i < 16; ++i) { tacc1[c][i] = 0ull; tacc2[c][i] = 0ull; }
         auto flush_stats = [&](int n_img) {
-            float s1, s2;
-            epi_flush(tacc1, tacc2, lane, s1, s2);
-            double *s = p.stats + ((long long)n_img * p.Cout + nt * BN + col0 + lane) * 2;
-            atomicAdd(s, (double)s1);
-            atomicAdd(s + 1, (double)s2);
+#pragma unroll
+            for (int c = 0; c < kChunks; ++c) {
+                float s1, s2;
+                epi_flush(tacc1[c], tacc2[c], lane, s1, s2);
+                double *s = p.stats + ((long long)n_img * p.Cout + nt * BN + col0 + c * 32 + lane) * 2;
+                atomicAdd(s, (double)s1);
+                atomicAdd(s + 1, (double)s2);
+            }
         };
         int cur_n = -1;
-        long long w_epi = 0, x_wait = 0, x_work = 0;
-        // epilogue tile walker (coordinates advance with carries, no divisions in the loop)
-        const int estep = kSplit ? 1 : 2;
+        long long w_epi = 0;
+        // tile walker (coordinates advance with carries, no divisions in the loop)
+        const int estep = kAltTiles ? 2 : 1;
         const int esx = estep % p.tiles_x, esy = (estep / p.tiles_x) % p.tiles_y, esn = estep / tiles_per_img;
-        int e_tile = t_begin + (kSplit ? 0 : grp);
+        int e_tile = t_begin + (kAltTiles ? grp : 0);
         int tx = e_tile % p.tiles_x, ty = (e_tile / p.tiles_x) % p.tiles_y, n = e_tile / tiles_per_img + p.n_base;
-        // transform state
-        constexpr int kCpp = KC / 8;                                             // 16-byte chunks (8 channels) per halo pixel
-        constexpr int kIters = (kHaloPix * kCpp + kHaloWorkers - 1) / kHaloWorkers;     // chunks per thread per halo: 3 (KC=32) or 6 (KC=64)
-        constexpr int kBatch = 3;
-        constexpr uint32_t kXorMask = (KC == 64) ? 7u : 3u;
-        const int cb = wt % kCpp;                                                // 256 % kCpp == 0: a thread keeps ONE channel block
-        // tile-invariant per-chunk data: byte offset inside a stage (absolute-address swizzle: the stage base is 1024-byte
-        // aligned, so chunk index XOR ((row offset >> 7) & mask)) | halo x << 16 | halo y << 20
-        uint32_t meta[kIters];
-#pragma unroll
-        for (int i = 0; i < kIters; ++i) {
-            const int pix = (wt + i * kHaloWorkers) / kCpp;
-            const uint32_t row_off = (uint32_t)(pix * kRowB);
-            const uint32_t sw = (row_off >> 7) & kXorMask;
-            meta[i] = pix < kHaloPix ? ((row_off + (((uint32_t)cb ^ sw) << 4)) | ((uint32_t)(pix % kHaloW) << 16) | ((uint32_t)(pix / kHaloW) << 20)) : 0xFFFFFFFFu;
-        }
-        int xtx = t_begin % p.tiles_x, xty = (t_begin / p.tiles_x) % p.tiles_y, xn = t_begin / tiles_per_img + p.n_base;
-        int xf_n = -1, xstage = 0;
-        uint32_t xphase = 0;
-        const float slope = p.in_slope;
-
         const int n_local = t_end - t_begin;
-        for (int j = 0; j < n_local + kLag; ++j) {
-            if (FUSE && j < n_local) {
-                // ---------------- transform the halo(s) of local tile j ----------------
-                if (xn != xf_n) {
-                    // scale / shift of the producer's InstanceNorm for image xn, all Cin channels: same arithmetic as norm_act_kernel
-                    // (double mean / rstd, one rounding to float), once per image and CTA
-                    named_bar_sync(1, kHaloWorkers);
-                    for (int c = wt; c < p.Cin; c += kHaloWorkers) {
-                        const double *st = p.in_stats + ((long long)xn * p.Cin + c) * 2;
-                        const double mean = st[0] / (double)p.in_hw;
-                        const double var = fmax(st[1] / (double)p.in_hw - mean * mean, 0.0);
-                        const double rstd = 1.0 / sqrt(var + (double)p.in_eps);
-                        const float g = p.in_gamma ? __ldg(p.in_gamma + c) : 1.f, b = p.in_beta ? __ldg(p.in_beta + c) : 0.f;
-                        s_ss[c] = (float)(rstd * (double)g);
-                        s_ss[p.Cin + c] = (float)((double)b - mean * rstd * (double)g);
-                    }
-                    named_bar_sync(1, kHaloWorkers);
-                    xf_n = xn;
-                }
-                // halo pixel (hx, hy) is image pixel (xtx*8 - 1 + hx, xty*16 - 1 + hy)
-                const int hx_lo = 1 - xtx * 8, hx_hi = p.W + 1 - xtx * 8, hy_lo = 1 - xty * 16, hy_hi = p.H + 1 - xty * 16;
-                for (int cc = 0; cc < p.cin_chunks; ++cc) {
-                    float scs[8], shs[8];
-                    {
-                        const float4 *ps = reinterpret_cast<const float4 *>(s_ss + cc * KC + cb * 8);
-                        const float4 *ph = reinterpret_cast<const float4 *>(s_ss + p.Cin + cc * KC + cb * 8);
-                        const float4 a0 = ps[0], a1 = ps[1], b0 = ph[0], b1 = ph[1];
-                        scs[0] = a0.x; scs[1] = a0.y; scs[2] = a0.z; scs[3] = a0.w; scs[4] = a1.x; scs[5] = a1.y; scs[6] = a1.z; scs[7] = a1.w;
-                        shs[0] = b0.x; shs[1] = b0.y; shs[2] = b0.z; shs[3] = b0.w; shs[4] = b1.x; shs[5] = b1.y; shs[6] = b1.z; shs[7] = b1.w;
-                    }
-                    const long long tq0 = p.dbg_out ? clock64() : 0;
-                    mbar_wait(&full_bar[xstage], xphase);
-                    const long long tq1 = p.dbg_out ? clock64() : 0;
-                    x_wait += tq1 - tq0;
-                    uint8_t *base = smem_a + xstage * kStageBytes;
-#pragma unroll
-                    for (int b0 = 0; b0 < kIters; b0 += kBatch) {
-                        if (p.dbg & 64) break;
-                        // all loads of a batch first, then the arithmetic, then the stores (the loop is latency bound otherwise)
-                        uint4 v[kBatch];
-                        bool ok[kBatch];
-#pragma unroll
-                        for (int i = 0; i < kBatch; ++i) {
-                            const uint32_t m = meta[b0 + i];
-                            const int hx = (int)((m >> 16) & 15u), hy = (int)((m >> 20) & 31u);
-                            // outside the image TMA wrote zeros = the conv padding of the NORMALISED tensor: leave them
-                            ok[i] = m != 0xFFFFFFFFu && hx >= hx_lo && hx < hx_hi && hy >= hy_lo && hy < hy_hi;
-                            if (ok[i]) v[i] = *reinterpret_cast<const uint4 *>(base + (m & 0xFFFFu));
-                        }
-#pragma unroll
-                        for (int i = 0; i < kBatch; ++i) {
-                            if (!ok[i]) continue;
-                            uint32_t *w = reinterpret_cast<uint32_t *>(&v[i]);
-#pragma unroll
-                            for (int k = 0; k < 4; ++k) {
-                                const float2 f = unpack2<DT>(w[k]);
-                                float y0 = fmaf(f.x, scs[2 * k], shs[2 * k]), y1 = fmaf(f.y, scs[2 * k + 1], shs[2 * k + 1]);
-                                y0 = y0 > 0.f ? y0 : y0 * slope;
-                                y1 = y1 > 0.f ? y1 : y1 * slope;
-                                w[k] = pack2<DT>(y0, y1);
-                            }
-                        }
-#pragma unroll
-                        for (int i = 0; i < kBatch; ++i)
-                            if (ok[i]) *reinterpret_cast<uint4 *>(base + (meta[b0 + i] & 0xFFFFu)) = v[i];
-                    }
-                    if (!(p.dbg & 32)) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic-proxy writes -> visible to the MMA (async proxy)
-                    mbar_arrive(&ready_bar[xstage]);
-                    if (p.dbg_out) x_work += clock64() - tq1;
-                    if (++xstage == p.n_stages) { xstage = 0; xphase ^= 1; }
-                }
-                if (++xtx == p.tiles_x) { xtx = 0; if (++xty == p.tiles_y) { xty = 0; ++xn; } }
-            }
-            // ---------------- epilogue of local tile e = j - kLag ----------------
-            const int e = j - kLag;
-            if (e < 0 || !(kSplit || (e & 1) == grp)) continue;
+        for (int e = kAltTiles ? grp : 0; e < n_local; e += estep) {
             const int buf = e & 1;
             const uint32_t par = (uint32_t)(e >> 1) & 1u;
             const int x = tx * 8 + ix, y = ty * 16 + iy;
@@ -339,24 +215,29 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 cur_n = n;
             }
             const long long tw0 = p.dbg_out ? clock64() : 0;
-            mbar_wait(&tmem_full[buf], par);
+            mbar_wait_parked(&tmem_full[buf], par);
             if (p.dbg_out) w_epi += clock64() - tw0;
             tcgen05_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BN + col0);
             DT *dst = out + (((long long)n * p.H + y) * p.W + x) * p.out_ps + nt * BN + col0;
-            uint32_t r[32];
-            tmem_ld_32x32b_x32(taddr, r);
-            tmem_ld_wait();
-            tcgen05_fence_before();
-            mbar_arrive(&tmem_empty[buf]);        // this thread's TMEM reads of the tile are done
-            uint32_t pk[16];
-            epi_chunk<DT>(r, s_bias + col0, pk, tacc1, tacc2, do_stats && valid);
-            if (valid) {
-                // 2 x 32-byte stores (STG.256): every sector is written whole by one instruction
 #pragma unroll
-                for (int k = 0; k < 2; ++k)
-                    asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst + 16 * k), "r"(pk[8 * k]), "r"(pk[8 * k + 1]),
-                                 "r"(pk[8 * k + 2]), "r"(pk[8 * k + 3]), "r"(pk[8 * k + 4]), "r"(pk[8 * k + 5]), "r"(pk[8 * k + 6]), "r"(pk[8 * k + 7]) : "memory");
+            for (int c = 0; c < kChunks; ++c) {
+                uint32_t r[32];
+                tmem_ld_32x32b_x32(taddr + c * 32, r);
+                tmem_ld_wait();
+                if (c == kChunks - 1) {
+                    tcgen05_fence_before();
+                    mbar_arrive(&tmem_empty[buf]);        // this thread's TMEM reads of the tile are done
+                }
+                uint32_t pk[16];
+                epi_chunk<DT>(r, s_bias + col0 + c * 32, pk, tacc1[c], tacc2[c], do_stats && valid);
+                if (valid) {
+                    // 2 x 32-byte stores (STG.256): every sector is written whole by one instruction
+#pragma unroll
+                    for (int k = 0; k < 2; ++k)
+                        asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst + c * 32 + 16 * k), "r"(pk[8 * k]), "r"(pk[8 * k + 1]),
+                                     "r"(pk[8 * k + 2]), "r"(pk[8 * k + 3]), "r"(pk[8 * k + 4]), "r"(pk[8 * k + 5]), "r"(pk[8 * k + 6]), "r"(pk[8 * k + 7]) : "memory");
+                }
             }
             tx += esx; if (tx >= p.tiles_x) { tx -= p.tiles_x; ++ty; }
             ty += esy; if (ty >= p.tiles_y) { ty -= p.tiles_y; ++n; }
@@ -365,12 +246,209 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (do_stats && cur_n >= 0) flush_stats(cur_n);
         if (p.dbg_out && wt == 0) {
             unsigned long long *o = p.dbg_out + (size_t)(blockIdx.y * gridDim.x + blockIdx.x) * 8;
-            o[3] = (unsigned long long)w_epi; o[4] = (unsigned long long)x_wait; o[5] = (unsigned long long)x_work;
+            o[3] = (unsigned long long)w_epi;
+        }
+    } else if (FUSE && warp < kEpiWarps + kHaloXformThreads / 32) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 96;");
+        // ===================== transform warps (4..11): y = leaky(x * scale[n][c] + shift[n][c]) on every halo stage, in place =====================
+        // The 256 threads split the pixels of every stage (short latency per stage: the ring holds only 3 - 6 stages); a thread owns one
+        // 16-byte channel block, its 8 scale / shift pairs live in registers.  Straight-line code: a batch = 4 loads, 16 independent
+        // fp32x2 chains, 4 predicated stores; only border tiles test the pixel position.
+        const int xt = threadIdx.x - 128;                                        // 0..255
+        constexpr int kCpp = KC / 8;                                             // 16-byte chunks (8 channels) per halo pixel
+        constexpr int kPixStep = kHaloXformThreads / kCpp;                       // halo pixels covered per step: 64 (KC=32) or 32 (KC=64)
+        constexpr int kIters = (kHaloPix + kPixStep - 1) / kPixStep;             // steps per stage: 3 or 6 (the last one is partial)
+        constexpr int kBatch = 4;
+        constexpr uint32_t kXorMask = (KC == 64) ? 7u : 3u;
+        const int cb = xt % kCpp;                                                // the thread's channel block (256 % kCpp == 0)
+        // tile-invariant per-step data: byte offset inside a stage (absolute-address swizzle: the stage base is 1024-byte aligned, so
+        // chunk index XOR ((row offset >> 7) & mask)) | halo x << 16 | halo y << 20 | bit 31: no pixel (offset 0)
+        uint32_t meta[kIters];
+#pragma unroll
+        for (int i = 0; i < kIters; ++i) {
+            const int pix = xt / kCpp + i * kPixStep;
+            const uint32_t row_off = (uint32_t)(pix * kRowB);
+            const uint32_t sw = (row_off >> 7) & kXorMask;
+            meta[i] = pix < kHaloPix ? ((row_off + (((uint32_t)cb ^ sw) << 4)) | ((uint32_t)(pix % kHaloW) << 16) | ((uint32_t)(pix / kHaloW) << 20)) : 0x80000000u;
+        }
+        int xtx = t_begin % p.tiles_x, xty = (t_begin / p.tiles_x) % p.tiles_y, xn = t_begin / tiles_per_img + p.n_base;
+        int xf_n = -1, xstage = 0;
+        uint32_t xphase = 0;
+        const uint64_t slope2 = f32x2_pack(p.in_slope, p.in_slope);
+        long long x_wait = 0, x_work = 0;
+        for (int tile = t_begin; tile < t_end; ++tile) {
+            if (xn != xf_n) {
+                // scale / shift of the producer's InstanceNorm for image xn, all Cin channels: same arithmetic as norm_act_kernel
+                // (double mean / rstd, one rounding to float), once per image and CTA
+                named_bar_sync(1, kHaloXformThreads);
+                for (int c = xt; c < p.Cin; c += kHaloXformThreads) {
+                    const double *st = p.in_stats + ((long long)xn * p.Cin + c) * 2;
+                    const double mean = st[0] / (double)p.in_hw;
+                    const double var = fmax(st[1] / (double)p.in_hw - mean * mean, 0.0);
+                    const double rstd = 1.0 / sqrt(var + (double)p.in_eps);
+                    const float ga = p.in_gamma ? __ldg(p.in_gamma + c) : 1.f, be = p.in_beta ? __ldg(p.in_beta + c) : 0.f;
+                    s_ss[c] = (float)(rstd * (double)ga);
+                    s_ss[kHaloMaxCin + c] = (float)((double)be - mean * rstd * (double)ga);
+                }
+                named_bar_sync(1, kHaloXformThreads);
+                xf_n = xn;
+            }
+            // halo pixel (hx, hy) is image pixel (xtx*8 - 1 + hx, xty*16 - 1 + hy); outside the image TMA wrote zeros = the conv padding
+            // of the NORMALISED tensor: those pixels are left alone
+            const int hx_lo = 1 - xtx * 8, hx_hi = p.W + 1 - xtx * 8, hy_lo = 1 - xty * 16, hy_hi = p.H + 1 - xty * 16;
+            const bool interior = hx_lo <= 0 && hx_hi >= kHaloW && hy_lo <= 0 && hy_hi >= kHaloH;       // warp-uniform: no per-pixel test
+            for (int cc = 0; cc < p.cin_chunks; ++cc) {
+                uint64_t sc2[4], sh2[4];
+                {
+                    const float4 *ps = reinterpret_cast<const float4 *>(s_ss + cc * KC + cb * 8);
+                    const float4 *ph = reinterpret_cast<const float4 *>(s_ss + kHaloMaxCin + cc * KC + cb * 8);
+                    const float4 a0 = ps[0], a1 = ps[1], b0 = ph[0], b1 = ph[1];
+                    sc2[0] = f32x2_pack(a0.x, a0.y); sc2[1] = f32x2_pack(a0.z, a0.w); sc2[2] = f32x2_pack(a1.x, a1.y); sc2[3] = f32x2_pack(a1.z, a1.w);
+                    sh2[0] = f32x2_pack(b0.x, b0.y); sh2[1] = f32x2_pack(b0.z, b0.w); sh2[2] = f32x2_pack(b1.x, b1.y); sh2[3] = f32x2_pack(b1.z, b1.w);
+                }
+                const long long tq0 = p.dbg_out ? clock64() : 0;
+                mbar_wait_parked(&full_bar[xstage], xphase);
+                const long long tq1 = p.dbg_out ? clock64() : 0;
+                x_wait += tq1 - tq0;
+                const uint32_t sbase = smem_u32(smem_a) + (uint32_t)(xstage * kStageBytes);
+                auto run_stage = [&](auto check_tag) {
+                    constexpr bool kCheck = decltype(check_tag)::value;
+#pragma unroll
+                    for (int b0 = 0; b0 < kIters; b0 += kBatch) {
+                        uint4 v[kBatch];
+                        bool ok[kBatch];
+#pragma unroll
+                        for (int i = 0; i < kBatch; ++i) {
+                            if (b0 + i >= kIters) continue;
+                            const uint32_t m = meta[b0 + i];
+                            ok[i] = (b0 + i < kIters - 1) || !(m & 0x80000000u);          // compile-time true except in the last step
+                            if (kCheck) {
+                                const int hx = (int)((m >> 16) & 15u), hy = (int)((m >> 20) & 31u);
+                                ok[i] = ok[i] && hx >= hx_lo && hx < hx_hi && hy >= hy_lo && hy < hy_hi;
+                            }
+#ifdef TS2D_HALO_PROBE
+                            if (p.dbg & 128) { v[i] = make_uint4(m, m * 3u, m * 5u, m * 7u); continue; }      // probe: no shared-memory loads
+#endif
+                            v[i] = lds128(sbase + (m & 0xFFFFu));                        // (a thread without a pixel reads chunk 0: harmless)
+                        }
+#pragma unroll
+                        for (int i = 0; i < kBatch; ++i) {
+                            if (b0 + i >= kIters) continue;
+                            uint32_t *w = reinterpret_cast<uint32_t *>(&v[i]);
+#ifdef TS2D_HALO_PROBE
+                            if (p.dbg & 256) continue;                                                             // probe: no arithmetic
+#endif
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) {
+                                const float2 f = unpack2<DT>(w[k]);
+                                // same roundings as norm_act_kernel: fma, then y > 0 ? y : y * slope (== max(y, y * slope) for 0 <= slope <= 1)
+                                const uint64_t y = f32x2_fma(f32x2_pack(f.x, f.y), sc2[k], sh2[k]);
+                                const uint64_t ys = f32x2_mul(y, slope2);
+                                w[k] = pack2<DT>(fmaxf(f32x2_lo(y), f32x2_lo(ys)), fmaxf(f32x2_hi(y), f32x2_hi(ys)));
+                            }
+                        }
+#pragma unroll
+                        for (int i = 0; i < kBatch; ++i) {
+                            if (b0 + i >= kIters) continue;
+#ifdef TS2D_HALO_PROBE
+                            if ((p.dbg & 128) && v[i].x != 0x12345u) continue;                                    // probe: (practically) no stores
+#endif
+                            if (ok[i]) sts128(sbase + (meta[b0 + i] & 0xFFFFu), v[i]);
+                        }
+                    }
+                };
+                if (!(p.dbg & 64)) {
+                    if (interior) run_stage(std::false_type{});
+                    else run_stage(std::true_type{});
+                }
+                if (!(p.dbg & 32)) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic-proxy writes -> visible to the MMA (async proxy)
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&ready_bar[xstage]);
+                if (p.dbg_out) x_work += clock64() - tq1;
+                if (++xstage == p.n_stages) { xstage = 0; xphase ^= 1; }
+            }
+            if (++xtx == p.tiles_x) { xtx = 0; if (++xty == p.tiles_y) { xty = 0; ++xn; } }
+        }
+        if (p.dbg_out && xt == 0) {
+            unsigned long long *o = p.dbg_out + (size_t)(blockIdx.y * gridDim.x + blockIdx.x) * 8;
+            o[4] = (unsigned long long)x_wait; o[5] = (unsigned long long)x_work;
+        }
+    } else {
+        if constexpr (FUSE) asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
+        if (warp == kHaloWarpTma) {
+            // ===================== TMA producer =====================
+            if (lane == 0) {
+                mbar_expect_tx(w_bar, (uint32_t)w_bytes);
+                for (int cc = 0; cc < p.cin_chunks; ++cc)
+                    for (int tap = 0; tap < 9; ++tap)
+                        tma_load_3d(smem_w + (cc * 9 + tap) * kWBlock, &tmB, w_bar, cc * KC, nt * BN, tap);
+                griddep_wait();                             // the resident weights stream in while the previous launch drains
+                int stage = 0;
+                uint32_t phase = 0;
+                for (int tile = t_begin; tile < t_end; ++tile) {
+                    const int tx = tile % p.tiles_x, ty = (tile / p.tiles_x) % p.tiles_y, n = tile / tiles_per_img + p.n_base;
+                    for (int cc = 0; cc < p.cin_chunks; ++cc) {
+                        mbar_wait_parked(&empty_bar[stage], phase ^ 1);
+                        mbar_expect_tx(&full_bar[stage], kHaloBytes);
+                        if (p.dbg & 8) tma_load_4d(smem_a + stage * kStageBytes, &tmA, &full_bar[stage], cc * KC, -1, -1, p.n_base);
+                        else tma_load_4d(smem_a + stage * kStageBytes, &tmA, &full_bar[stage], cc * KC, tx * 8 - 1, ty * 16 - 1, n);
+                        if (++stage == p.n_stages) { stage = 0; phase ^= 1; }
+                    }
+                }
+            }
+        } else if (warp == kHaloWarpMma) {
+            // ===================== MMA issuer (whole warp convergent, one elected lane issues; see conv_tc.cuh) =====================
+            const uint32_t leader = elect_one();
+            const uint32_t idesc = make_idesc<DT>(BN);
+            constexpr uint32_t a_hi = desc_hi<KC>(kHaloW * kRowB);        // 8-row groups of the A view are one halo row (10 pixels) apart
+            constexpr uint32_t b_hi = desc_hi<KC>(KC == 64 ? 1024 : 512);
+            const uint32_t w_lo = desc_lo<KC>(smem_u32(smem_w));
+            const uint32_t a0_lo = desc_lo<KC>(smem_u32(smem_a));
+            mbar_wait(w_bar, 0);
+            tcgen05_fence_after();
+            int stage = 0;
+            uint32_t phase = 0;
+            int it = 0;
+            long long t_start = 0, w_halo = 0, w_tmem = 0;
+            if (p.dbg_out) t_start = clock64();
+            for (int tile = t_begin; tile < t_end; ++tile, ++it) {
+                const int buf = it & 1;
+                const uint32_t use = (uint32_t)(it >> 1);
+                long long t0 = p.dbg_out ? clock64() : 0;
+                mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);
+                if (p.dbg_out) w_tmem += clock64() - t0;
+                tcgen05_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(buf * BN);
+                for (int cc = 0; cc < p.cin_chunks; ++cc) {
+                    t0 = p.dbg_out ? clock64() : 0;
+                    mbar_wait(FUSE ? &ready_bar[stage] : &full_bar[stage], phase);
+                    if (p.dbg_out) w_halo += clock64() - t0;
+                    tcgen05_fence_after();
+                    const uint32_t a_lo = a0_lo + (uint32_t)(stage * (kStageBytes >> 4));
+                    const uint32_t b_lo = w_lo + (uint32_t)(cc * 9 * (kWBlock >> 4));
+    #pragma unroll
+                    for (int tap = 0; tap < 9; ++tap) {
+                        if ((p.dbg & 4) && tap) continue;
+                        const int r = tap / 3, s = tap % 3;
+    #pragma unroll
+                        for (int k = 0; k < KC / 16; ++k)
+                            tcgen05_mma_f16_lohi(leader, d_tmem, a_lo + (uint32_t)((((r * kHaloW + s) * kRowB) >> 4) + k * 2), a_hi,
+                                                 b_lo + (uint32_t)(((tap * kWBlock) >> 4) + k * 2), b_hi, idesc, (tap | k) ? 1u : (uint32_t)(cc != 0));
+                    }
+                    tcgen05_commit_pred(leader, &empty_bar[stage]);
+                    if (++stage == p.n_stages) { stage = 0; phase ^= 1; }
+                }
+                tcgen05_commit_pred(leader, &tmem_full[buf]);
+            }
+            if (p.dbg_out && leader) {
+                unsigned long long *o = p.dbg_out + (size_t)(blockIdx.y * gridDim.x + blockIdx.x) * 8;
+                o[0] = (unsigned long long)(clock64() - t_start); o[1] = (unsigned long long)w_halo; o[2] = (unsigned long long)w_tmem;
+            }
         }
     }
     tcgen05_fence_before();
     __syncthreads();
-    if (warp == 1) {
+    if (warp == kHaloWarpMma) {
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kTmemCols) : "memory");
     }
 }

@@ -95,6 +95,27 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
         "DONE:\n"
         "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
+#ifndef TS2D_PARK_NS
+#define TS2D_PARK_NS 64
+#endif
+// Same wait for roles that are NOT latency critical (epilogue warps waiting for an accumulator, the TMA producer waiting for a free
+// slot): try_wait with a suspend-time hint parks the warp in hardware instead of spinning.  A spinning warp takes issue slots from the
+// warps that share its scheduler - measured on conv_halo_kernel<FUSE>: the transform warps (2, 3) share schedulers with four spinning
+// epilogue warps and ran at ~0.3 instructions per cycle (profiles/r02e_halo_bench_fuse.txt).
+__device__ __forceinline__ void mbar_wait_parked(uint64_t *bar, uint32_t parity) {
+#ifdef TS2D_MBAR_SPIN_LIMIT
+    mbar_wait(bar, parity);
+#else
+    uint32_t ok;
+    asm volatile("{\n.reg .pred P1;\nmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\nselp.u32 %0, 1, 0, P1;\n}"
+                 : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    while (!ok) {
+        __nanosleep(TS2D_PARK_NS);
+        asm volatile("{\n.reg .pred P1;\nmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\nselp.u32 %0, 1, 0, P1;\n}"
+                     : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    }
+#endif
+}
 __device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *tm, uint64_t *bar, int c0, int c1, int c2) {
     asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
                  ::"r"(smem_u32(dst)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2) : "memory");

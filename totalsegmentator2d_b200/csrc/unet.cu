@@ -343,7 +343,7 @@ static int launch_halo_inst(const CUtensorMap &tmA, const CUtensorMap &tmB, cons
     const int n_tiles_n = p.Cout / BN;
     const int total = p.tiles_x * p.tiles_y * p.N;
     const int gx = std::max(1, std::min(total, kNumSMs / n_tiles_n));
-    TS2D_CHECK_CUDA(launch_pdl(conv_halo_kernel<BN, KC, DT, FUSE>, dim3(gx, n_tiles_n), dim3(kHaloThreads), smem, st, tmA, tmB, p));
+    TS2D_CHECK_CUDA(launch_pdl(conv_halo_kernel<BN, KC, DT, FUSE>, dim3(gx, n_tiles_n), dim3(halo_threads<FUSE>()), smem, st, tmA, tmB, p));
     TS2D_LAUNCH_CHECK();
     return TS2D_OK;
 }
@@ -721,18 +721,20 @@ extern "C" int ts2d_unet_finalize(ts2d_unet *u) {
         c.defer = false; c.prod = -1;
     }
     // ---- deferred normalisation: producer writes raw + statistics only, the consumer normalises while loading ----
-    // TS2D_FUSE_NORM: 0 = every layer runs norm_act_kernel; 1 (default) = the last decoder conv is normalised inside the blend
-    // kernel; 2 = additionally conv_halo_kernel<FUSE> consumers (correct and bit-identical, but measured slower than the
-    // HBM-bound norm pass it replaces: the in-smem transform costs as many issue slots as the epilogue, see profiles/)
+    // TS2D_FUSE_NORM: 0 = every layer runs norm_act_kernel; 1 = the last decoder conv is normalised inside the blend kernel;
+    // 2 = additionally every conv_halo_kernel<FUSE> consumer (bit-identical; the transform warps rewrite the halo in shared memory);
+    // 3 (default) = like 2 but only consumers with 32 output channels per CTA, the only ones where the fused kernel beats
+    // conv + norm pass (profiles/r02m_halo_bench_fuse.txt: 512^2 32->32 0.168 ms against 0.111 + 0.079; 64-channel blocks break even)
     {
-        const int fuse = getenv("TS2D_FUSE_NORM") ? atoi(getenv("TS2D_FUSE_NORM")) : 1;
+        const int fuse = getenv("TS2D_FUSE_NORM") ? atoi(getenv("TS2D_FUSE_NORM")) : 3;
         for (size_t i = 0; i < u->convs.size(); ++i) u->convs[i].out_raw = (i & 1) ? u->rawB : u->raw;
         size_t k = 0;
         auto stage_pass = [&](int n_convs) {
             for (int i = 0; i + 1 < n_convs; ++i) {
                 ConvLayer &prod = u->convs[k + i], &cons = u->convs[k + i + 1];
-                // the fused kernel's workers run the epilogue of tile j-2 after the transform of tile j: the ring must hold a whole tile
-                if (fuse >= 2 && cons.halo && pl.precision != TS2D_PREC_F32 && cons.halo_stages >= cons.cin / cons.kc && cons.cin <= 256) {
+                // the transform computes leaky(y) as max(y, y * slope): exact for slopes in [0, 1] only
+                if (fuse >= 2 && cons.halo && pl.precision != TS2D_PREC_F32 && cons.cin <= kHaloMaxCin && pl.negative_slope >= 0.f && pl.negative_slope <= 1.f &&
+                    (fuse == 2 || cons.halo_bn == 32)) {
                     prod.defer = true;
                     cons.prod = (int)(k + i);
                     cons.in = prod.out_raw; cons.in_ps = prod.cout;
