@@ -60,7 +60,7 @@ static float run(const Layer &L, int stages, int dbg, bool timing, int reps, __n
     }
     ConvHaloParams p;
     memset(&p, 0, sizeof(p));
-    p.N = L.N; p.H = L.H; p.W = L.W; p.Cout = L.Cout; p.cin_chunks = L.Cin / KC;
+    p.N = L.N; p.H = L.H; p.W = L.W; p.Cout = L.Cout; p.cin_chunks = L.Cin / KC; p.split_chunks = p.cin_chunks;
     p.tiles_x = (L.W + 7) / 8; p.tiles_y = (L.H + 15) / 16; p.n_stages = stages;
     p.out_ps = L.Cout; p.out = out; p.bias = bias; p.stats = stats; p.Cin = L.Cin;
     p.dbg = dbg; p.dbg_out = timing ? dbg_out : nullptr;
@@ -77,7 +77,7 @@ static float run(const Layer &L, int stages, int dbg, bool timing, int reps, __n
     for (int r = 0; r < reps + 2; ++r) {
         CK(cudaMemsetAsync(stats, 0, (size_t)L.N * L.Cout * 2 * sizeof(double)));
         CK(cudaEventRecord(e0));
-        conv_halo_kernel<BN, KC, __nv_bfloat16, FUSE><<<dim3(gx, nt), halo_threads<FUSE>(), smem>>>(tmA, tmB, p);
+        conv_halo_kernel<BN, KC, __nv_bfloat16, FUSE><<<dim3(gx, nt), halo_threads<FUSE>(), smem>>>(tmA, tmA, tmB, p);
         CK(cudaEventRecord(e1));
         CK(cudaEventSynchronize(e1));
         CK(cudaGetLastError());

@@ -45,6 +45,7 @@ struct ConvHaloParams {
     int N, H, W, Cout;          // images, output grid (== input grid), output channels
     int n_base;                 // first image of this launch (chunked execution over the batch)
     int cin_chunks;             // Cin / KC
+    int split_chunks;           // halo chunks [0, split_chunks) come from tmA, the rest from tmA2 (see ConvTcParams); == cin_chunks for one input
     int tiles_x, tiles_y;       // ceil(W/8), ceil(H/16)
     int n_stages;               // halo ring depth (host: what fits beside the resident weights)
     long long out_ps;           // output pixel stride in elements
@@ -99,7 +100,7 @@ __device__ __forceinline__ void named_bar_sync(int id, int threads) { asm volati
 
 template <int BN, int KC, typename DT, bool FUSE>
 __global__ void __launch_bounds__(halo_threads<FUSE>(), 1)
-conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const ConvHaloParams p) {
+conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB, const ConvHaloParams p) {
     static_assert(BN == 32 || BN == 64, "conv_halo_kernel: BN must be 32 or 64");
     constexpr int kRowB = KC * 2;                      // bytes per pixel row of the operand
     constexpr int kHaloBytes = kHaloPix * kRowB;       // bytes TMA delivers per halo
@@ -132,6 +133,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
     if (warp == kHaloWarpTma && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA2) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
         for (int s = 0; s < p.n_stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); mbar_init(&ready_bar[s], kHaloXformThreads / 32); }      // one elected arrival per transform warp
         for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], (!FUSE && kSplit) ? 256 : 128); }
@@ -391,7 +393,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         mbar_wait_parked(&empty_bar[stage], phase ^ 1);
                         mbar_expect_tx(&full_bar[stage], kHaloBytes);
                         if (p.dbg & 8) tma_load_4d(smem_a + stage * kStageBytes, &tmA, &full_bar[stage], cc * KC, -1, -1, p.n_base);
-                        else tma_load_4d(smem_a + stage * kStageBytes, &tmA, &full_bar[stage], cc * KC, tx * 8 - 1, ty * 16 - 1, n);
+                        else if (cc < p.split_chunks) tma_load_4d(smem_a + stage * kStageBytes, &tmA, &full_bar[stage], cc * KC, tx * 8 - 1, ty * 16 - 1, n);
+                        else tma_load_4d(smem_a + stage * kStageBytes, &tmA2, &full_bar[stage], (cc - p.split_chunks) * KC, tx * 8 - 1, ty * 16 - 1, n);
                         if (++stage == p.n_stages) { stage = 0; phase ^= 1; }
                     }
                 }

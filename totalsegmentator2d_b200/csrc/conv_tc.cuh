@@ -32,6 +32,8 @@ namespace ts2d {
 struct ConvTcParams {
     int N, Hout, Wout, Cout;     // GEMM-side output grid (for transposed conv: the INPUT grid)
     int cin_chunks;              // Cin / KC
+    int split_chunks;            // K-chunks [0, split_chunks) of a tap come from tmA, the rest from tmA2 (decoder convs: the up-sampled tensor and the
+                                 // encoder skip are two dense tensors instead of one concatenated buffer); == cin_chunks when there is one input
     int taps, kw;                // taps = kh*kw (1 for 1x1 / transposed conv slices)
     int pad_h, pad_w;
     int stride2;                 // 0: stride 1 (4-D map); else the 5-D parity map, bit 0 = stride 2 along w, bit 1 = stride 2 along h
@@ -331,7 +333,7 @@ __device__ __forceinline__ float warp_transpose_sum32(float (&x)[32], int lane) 
 
 template <int BN, int KC, typename DT>
 __global__ void __launch_bounds__(kTcThreads, 1)
-conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const ConvTcParams p) {
+conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB, const ConvTcParams p) {
     constexpr int kStages = tc_num_stages<BN, KC>();
     constexpr int kABytes = 128 * KC * 2;
     constexpr int kStageBytes = tc_stage_bytes<BN, KC>();
@@ -355,6 +357,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA2) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
         for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], p.mc ? 2 : 1); }      // mc: both CTAs' MMAs free a slot
         for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], kAlt ? 128 : 256); }
@@ -405,7 +408,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     uint8_t *sb = sa + kABytes;
                     mbar_expect_tx(&full_bar[stage], kStageBytes);
                     if (!p.stride2) {
-                        tma_load_4d(sa, &tmA, &full_bar[stage], cc * KC, x0 + s - p.pad_w, y0 + r - p.pad_h, n0);
+                        if (cc < p.split_chunks) tma_load_4d(sa, &tmA, &full_bar[stage], cc * KC, x0 + s - p.pad_w, y0 + r - p.pad_h, n0);
+                        else tma_load_4d(sa, &tmA2, &full_bar[stage], (cc - p.split_chunks) * KC, x0 + s - p.pad_w, y0 + r - p.pad_h, n0);
                     } else {
                         // input row 2*oy + r - pad = 2*h2 + py ; input col 2*ox + s - pad = 2*w2 + px
                         const int dr = r - p.pad_h, ds = s - p.pad_w;

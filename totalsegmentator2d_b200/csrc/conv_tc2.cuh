@@ -24,7 +24,7 @@ template <int BN, int KC> constexpr int tc2_smem_bytes() { return tc2_num_stages
 
 template <int BN, int KC, typename DT>
 __global__ void __launch_bounds__(kTcThreads, 1)
-conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const ConvTcParams p) {
+conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB, const ConvTcParams p) {
     static_assert(BN == 128 || BN == 256, "conv_tc2_kernel: BN must be 128 or 256");
     constexpr int kStages = tc2_num_stages<BN, KC>();
     constexpr int kABytes = 128 * KC * 2;                    // one pixel tile
@@ -46,6 +46,7 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA2) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
         for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
         for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], 256); }
@@ -91,7 +92,8 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 #pragma unroll
                     for (int t = 0; t < 2; ++t) {
                         if (!p.stride2) {
-                            tma_load_4d(sa + t * kABytes, &tmA, &full_bar[stage], cc * KC, x0[t] + s - p.pad_w, y0[t] + r - p.pad_h, n0[t]);
+                            if (cc < p.split_chunks) tma_load_4d(sa + t * kABytes, &tmA, &full_bar[stage], cc * KC, x0[t] + s - p.pad_w, y0[t] + r - p.pad_h, n0[t]);
+                            else tma_load_4d(sa + t * kABytes, &tmA2, &full_bar[stage], (cc - p.split_chunks) * KC, x0[t] + s - p.pad_w, y0[t] + r - p.pad_h, n0[t]);
                         } else {
                             const int dr = r - p.pad_h, ds = s - p.pad_w;
                             const int py = (p.stride2 & 2) ? (dr & 1) : 0, px = (p.stride2 & 1) ? (ds & 1) : 0;

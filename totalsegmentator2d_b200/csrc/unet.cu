@@ -6,9 +6,11 @@
 // ConvTranspose2d(k = stride) -> cat(up, skip) -> conv blocks, 1x1 seg head (deep supervision off).
 //
 // Data layout in HBM (activations NHWC, element = plan precision):
-//   cat[l]   [N][H_l][W_l][2*C_l]   channels [0,C_l) = up-sampled decoder input, [C_l,2C_l) = encoder skip; the
-//                                   encoder writes its stage output straight into the skip half and the transposed
-//                                   conv writes straight into the other half: torch.cat never happens.
+//   skip[l]  [N][H_l][W_l][C_l]     encoder stage output (normalised), read by the next stage's strided conv and by the decoder
+//   up[l]    [N][H_l][W_l][C_l]     transposed-conv output.  torch.cat([up, skip]) never happens: the first decoder conv of a level
+//                                   takes its K-chunks from TWO tensor maps (channels [0,C_l) from up[l], [C_l,2C_l) from skip[l]).
+//                                   (Round 1 interleaved the two in one [..][2*C_l] buffer; at level 0 a half pixel is 64 bytes and the
+//                                   strided conv enc1.0 fetched 412 MB of DRAM for 201 MB of operand.)
 //   bott     [N][H_L][W_L][C_L]     bottleneck
 //   raw      conv output before normalisation (+ per-(n,c) sum / sum-of-squares in `stats`, double)
 //   tmpA/B   normalised intermediates / decoder stage outputs
@@ -55,12 +57,15 @@ struct ConvLayer {
     void *w_tc = nullptr;       // [tap][Cout][Cin] bf16/fp16
     const void *in = nullptr;   // set per forward for the first layer
     long long in_ps = 0;
+    const void *in2 = nullptr;  // decoder first convs: channels [c_split, cin) come from this tensor (the encoder skip)
+    long long in2_ps = 0;
+    int c_split = 0;            // channels taken from `in` (== cin when there is one input)
     void *norm_out = nullptr;
     long long out_ps = 0;
     double *stats = nullptr;
     bool tc = false;
     int bn = 0, kc = 0, enc_n = 0;
-    CUtensorMap tmA, tmB;
+    CUtensorMap tmA, tmA2, tmB;
     bool first = false;         // reads the caller's tiles: tmA encoded per forward
     bool halo = false;          // conv_halo_kernel (3x3 stride 1, halo tile + resident weights)
     int halo_bn = 0, halo_stages = 0;
@@ -106,7 +111,7 @@ struct ts2d_unet {
     // workspace
     uint8_t *arena = nullptr;
     size_t arena_bytes = 0;
-    std::vector<void *> cat;
+    std::vector<void *> skip, up;
     void *bott = nullptr, *raw = nullptr, *rawB = nullptr, *tmpA = nullptr, *tmpB = nullptr;
     float *partial = nullptr;     // split-K partial sums of the tiny levels [ksplit][N*HW][Cout] fp32
     size_t partial_bytes = 0;
@@ -245,7 +250,7 @@ static int encode_w_map(CUtensorMap *tm, const void *base, int Cin, int Cout, in
 }
 
 template <int BN, int KC, typename DT>
-static int launch_tc_inst(const CUtensorMap &tmA, const CUtensorMap &tmB, const ConvTcParams &p, cudaStream_t st) {
+static int launch_tc_inst(const CUtensorMap &tmA, const CUtensorMap &tmA2, const CUtensorMap &tmB, const ConvTcParams &p, cudaStream_t st) {
     static bool attr_set = false;
     constexpr int smem = tc_smem_bytes<BN, KC>();
     if (!attr_set) {
@@ -269,17 +274,17 @@ static int launch_tc_inst(const CUtensorMap &tmA, const CUtensorMap &tmB, const 
             max_clusters = std::min(n, kNumSMs / 2);
         }
         const int pairs = std::max(1, std::min(total / 2, max_clusters));
-        TS2D_CHECK_CUDA(launch_pdl_cluster(conv_tc_kernel<BN, KC, DT>, dim3(2 * pairs), dim3(kTcThreads), smem, st, 2, tmA, tmB, p));
+        TS2D_CHECK_CUDA(launch_pdl_cluster(conv_tc_kernel<BN, KC, DT>, dim3(2 * pairs), dim3(kTcThreads), smem, st, 2, tmA, tmA2, tmB, p));
         return TS2D_OK;
     }
     const int gx = std::max(1, std::min(total, kNumSMs));
-    TS2D_CHECK_CUDA(launch_pdl(conv_tc_kernel<BN, KC, DT>, dim3(gx), dim3(kTcThreads), smem, st, tmA, tmB, p));
+    TS2D_CHECK_CUDA(launch_pdl(conv_tc_kernel<BN, KC, DT>, dim3(gx), dim3(kTcThreads), smem, st, tmA, tmA2, tmB, p));
     TS2D_LAUNCH_CHECK();
     return TS2D_OK;
 }
 template <typename DT>
-static int launch_tc(int bn, int kc, const CUtensorMap &tmA, const CUtensorMap &tmB, const ConvTcParams &p, cudaStream_t st) {
-#define TS2D_TC_CASE(B, K) if (bn == B && kc == K) return launch_tc_inst<B, K, DT>(tmA, tmB, p, st);
+static int launch_tc(int bn, int kc, const CUtensorMap &tmA, const CUtensorMap &tmA2, const CUtensorMap &tmB, const ConvTcParams &p, cudaStream_t st) {
+#define TS2D_TC_CASE(B, K) if (bn == B && kc == K) return launch_tc_inst<B, K, DT>(tmA, tmA2, tmB, p, st);
     TS2D_TC_CASE(32, 32) TS2D_TC_CASE(64, 32) TS2D_TC_CASE(128, 32) TS2D_TC_CASE(256, 32)
     TS2D_TC_CASE(32, 64) TS2D_TC_CASE(64, 64) TS2D_TC_CASE(128, 64) TS2D_TC_CASE(256, 64)
 #undef TS2D_TC_CASE
@@ -288,7 +293,7 @@ static int launch_tc(int bn, int kc, const CUtensorMap &tmA, const CUtensorMap &
 }
 
 template <int BN, int KC, typename DT>
-static int launch_tc2_inst(const CUtensorMap &tmA, const CUtensorMap &tmB, const ConvTcParams &p, cudaStream_t st) {
+static int launch_tc2_inst(const CUtensorMap &tmA, const CUtensorMap &tmA2, const CUtensorMap &tmB, const ConvTcParams &p, cudaStream_t st) {
     static bool attr_set = false;
     constexpr int smem = tc2_smem_bytes<BN, KC>();
     if (!attr_set) {
@@ -297,14 +302,14 @@ static int launch_tc2_inst(const CUtensorMap &tmA, const CUtensorMap &tmB, const
     }
     const int units = (p.tiles_n * p.tiles_h * p.tiles_w / 2) * p.n_tiles_n;
     const int gx = std::max(1, std::min(units, kNumSMs));
-    TS2D_CHECK_CUDA(launch_pdl(conv_tc2_kernel<BN, KC, DT>, dim3(gx), dim3(kTcThreads), smem, st, tmA, tmB, p));
+    TS2D_CHECK_CUDA(launch_pdl(conv_tc2_kernel<BN, KC, DT>, dim3(gx), dim3(kTcThreads), smem, st, tmA, tmA2, tmB, p));
     TS2D_LAUNCH_CHECK();
     return TS2D_OK;
 }
 template <typename DT>
-static int launch_tc2(int bn, const CUtensorMap &tmA, const CUtensorMap &tmB, const ConvTcParams &p, cudaStream_t st) {
-    if (bn == 256) return launch_tc2_inst<256, 64, DT>(tmA, tmB, p, st);
-    if (bn == 128) return launch_tc2_inst<128, 64, DT>(tmA, tmB, p, st);
+static int launch_tc2(int bn, const CUtensorMap &tmA, const CUtensorMap &tmA2, const CUtensorMap &tmB, const ConvTcParams &p, cudaStream_t st) {
+    if (bn == 256) return launch_tc2_inst<256, 64, DT>(tmA, tmA2, tmB, p, st);
+    if (bn == 128) return launch_tc2_inst<128, 64, DT>(tmA, tmA2, tmB, p, st);
     set_error("no conv_tc2_kernel instantiation for BN=%d", bn);
     return TS2D_ERR_UNSUPPORTED;
 }
@@ -334,7 +339,7 @@ static int halo_smem_bytes(int cin, int bn, int kc, int stages) {
     return 1024 /*align*/ + w + stages * st + kHaloTailBytes;
 }
 template <int BN, int KC, typename DT, bool FUSE>
-static int launch_halo_inst(const CUtensorMap &tmA, const CUtensorMap &tmB, const ConvHaloParams &p, int smem, cudaStream_t st) {
+static int launch_halo_inst(const CUtensorMap &tmA, const CUtensorMap &tmA2, const CUtensorMap &tmB, const ConvHaloParams &p, int smem, cudaStream_t st) {
     static int attr_smem = 0;
     if (smem > attr_smem) {
         TS2D_CHECK_CUDA(cudaFuncSetAttribute(conv_halo_kernel<BN, KC, DT, FUSE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHaloSmemBudget));
@@ -343,15 +348,15 @@ static int launch_halo_inst(const CUtensorMap &tmA, const CUtensorMap &tmB, cons
     const int n_tiles_n = p.Cout / BN;
     const int total = p.tiles_x * p.tiles_y * p.N;
     const int gx = std::max(1, std::min(total, kNumSMs / n_tiles_n));
-    TS2D_CHECK_CUDA(launch_pdl(conv_halo_kernel<BN, KC, DT, FUSE>, dim3(gx, n_tiles_n), dim3(halo_threads<FUSE>()), smem, st, tmA, tmB, p));
+    TS2D_CHECK_CUDA(launch_pdl(conv_halo_kernel<BN, KC, DT, FUSE>, dim3(gx, n_tiles_n), dim3(halo_threads<FUSE>()), smem, st, tmA, tmA2, tmB, p));
     TS2D_LAUNCH_CHECK();
     return TS2D_OK;
 }
 template <typename DT>
-static int launch_halo(int bn, int kc, bool fuse, const CUtensorMap &tmA, const CUtensorMap &tmB, const ConvHaloParams &p, int smem, cudaStream_t st) {
+static int launch_halo(int bn, int kc, bool fuse, const CUtensorMap &tmA, const CUtensorMap &tmA2, const CUtensorMap &tmB, const ConvHaloParams &p, int smem, cudaStream_t st) {
 #define TS2D_HALO_CASE(B, K)                                                              \
-    if (bn == B && kc == K) return fuse ? launch_halo_inst<B, K, DT, true>(tmA, tmB, p, smem, st) \
-                                        : launch_halo_inst<B, K, DT, false>(tmA, tmB, p, smem, st);
+    if (bn == B && kc == K) return fuse ? launch_halo_inst<B, K, DT, true>(tmA, tmA2, tmB, p, smem, st) \
+                                        : launch_halo_inst<B, K, DT, false>(tmA, tmA2, tmB, p, smem, st);
     TS2D_HALO_CASE(32, 32) TS2D_HALO_CASE(64, 32) TS2D_HALO_CASE(32, 64) TS2D_HALO_CASE(64, 64)
 #undef TS2D_HALO_CASE
     set_error("no halo conv instantiation for BN=%d KC=%d", bn, kc);
@@ -498,6 +503,7 @@ static void fill_tc_params(ConvTcParams &p, int N, int Hout, int Wout, int cout,
     memset(&p, 0, sizeof(p));
     p.N = N; p.Hout = Hout; p.Wout = Wout; p.Cout = cout;
     p.cin_chunks = cin / kc;
+    p.split_chunks = p.cin_chunks;
     p.taps = taps; p.kw = kw; p.pad_h = pad_h; p.pad_w = pad_w;
     p.stride2 = stride2;
     p.in_ps = (int)in_ps;
@@ -641,8 +647,11 @@ extern "C" int ts2d_unet_finalize(ts2d_unet *u) {
     // ---- workspace ----
     auto align = [](size_t v) { return (v + 1023) & ~(size_t)1023; };
     size_t off = 0;
-    std::vector<size_t> cat_off(L - 1);
-    for (int l = 0; l < L - 1; ++l) { cat_off[l] = off; off += align((size_t)N * u->H[l] * u->W[l] * 2 * u->C[l] * es); }
+    std::vector<size_t> skip_off(L - 1), up_off(L - 1);
+    for (int l = 0; l < L - 1; ++l) {
+        skip_off[l] = off; off += align((size_t)N * u->H[l] * u->W[l] * u->C[l] * es);
+        up_off[l] = off; off += align((size_t)N * u->H[l] * u->W[l] * u->C[l] * es);
+    }
     const size_t bott_off = off; off += align((size_t)N * u->H[L - 1] * u->W[L - 1] * u->C[L - 1] * es);
     size_t max_act = 0;
     for (auto &c : u->convs) max_act = std::max(max_act, (size_t)N * c.Hout * c.Wout * c.cout * es);
@@ -663,8 +672,8 @@ extern "C" int ts2d_unet_finalize(ts2d_unet *u) {
     TS2D_CHECK_CUDA(cudaMalloc(&u->arena, off));
     TS2D_CHECK_CUDA(cudaMemset(u->arena, 0, off));
     u->arena_bytes = off;
-    u->cat.resize(L - 1);
-    for (int l = 0; l < L - 1; ++l) u->cat[l] = u->arena + cat_off[l];
+    u->skip.resize(L - 1); u->up.resize(L - 1);
+    for (int l = 0; l < L - 1; ++l) { u->skip[l] = u->arena + skip_off[l]; u->up[l] = u->arena + up_off[l]; }
     u->bott = u->arena + bott_off; u->raw = u->arena + raw_off; u->rawB = u->arena + rawb_off;
     u->feat_ss = reinterpret_cast<float *>(u->arena + ss_off); u->tmpA = u->arena + a_off; u->tmpB = u->arena + b_off;
     u->partial = max_partial ? reinterpret_cast<float *>(u->arena + partial_off) : nullptr;
@@ -680,10 +689,10 @@ extern "C" int ts2d_unet_finalize(ts2d_unet *u) {
     for (int s = 0; s < L; ++s) {
         for (int i = 0; i < pl.n_conv_enc[s]; ++i, ++ci) {
             ConvLayer &c = u->convs[ci];
-            c.in = cur; c.in_ps = cur_ps;
+            c.in = cur; c.in_ps = cur_ps; c.in2 = nullptr; c.in2_ps = 0; c.c_split = c.cin;
             const bool last = i == pl.n_conv_enc[s] - 1;
             if (last) {
-                if (s < L - 1) { c.norm_out = (uint8_t *)u->cat[s] + (size_t)u->C[s] * es; c.out_ps = 2 * u->C[s]; }
+                if (s < L - 1) { c.norm_out = u->skip[s]; c.out_ps = u->C[s]; }
                 else { c.norm_out = u->bott; c.out_ps = u->C[s]; }
             } else { c.norm_out = u->tmpA; c.out_ps = u->C[s]; }
             cur = c.norm_out; cur_ps = c.out_ps;
@@ -693,11 +702,12 @@ extern "C" int ts2d_unet_finalize(ts2d_unet *u) {
     for (int d = 0; d < L - 1; ++d) {
         const int l = L - 2 - d;
         UpLayer &up = u->ups[d];
-        up.in = lres; up.out = u->cat[l]; up.out_ps = 2 * u->C[l];
-        cur = u->cat[l]; cur_ps = 2 * u->C[l];
+        up.in = lres; up.out = u->up[l]; up.out_ps = u->C[l];
+        cur = u->up[l]; cur_ps = u->C[l];
         for (int i = 0; i < pl.n_conv_dec[d]; ++i, ++ci) {
             ConvLayer &c = u->convs[ci];
-            c.in = cur; c.in_ps = cur_ps;
+            c.in = cur; c.in_ps = cur_ps; c.in2 = nullptr; c.in2_ps = 0; c.c_split = c.cin;
+            if (i == 0) { c.in2 = u->skip[l]; c.in2_ps = u->C[l]; c.c_split = u->C[l]; }      // cat([up, skip]) as two K ranges
             const bool last = i == pl.n_conv_dec[d] - 1;
             c.norm_out = last ? u->tmpB : u->tmpA; c.out_ps = u->C[l];
             cur = c.norm_out; cur_ps = c.out_ps;
@@ -709,10 +719,10 @@ extern "C" int ts2d_unet_finalize(ts2d_unet *u) {
     // ---- parameters ----
     int rc;
     for (auto &c : u->convs) {
-        c.tc = tc_eligible(pl, c.cin, c.cout, c.kh, c.kw, c.sh, c.sw, c.Hin, c.Win, c.in_ps);
+        c.tc = tc_eligible(pl, c.cin, c.cout, c.kh, c.kw, c.sh, c.sw, c.Hin, c.Win, c.in_ps) && c.c_split % 32 == 0 && (c.in2 == nullptr || c.in2_ps % 8 == 0);
         if ((rc = repack_conv(c.w.host, c.cout, c.cin, c.kh * c.kw, false, pl.precision, c.tc, &c.w_direct, &c.w_tc))) return rc;
         if ((rc = upload(c.b)) || (rc = upload(c.gamma)) || (rc = upload(c.beta))) return rc;
-        if (c.tc) c.kc = (c.cin % 64 == 0) ? 64 : 32;
+        if (c.tc) c.kc = (c.c_split % 64 == 0 && (c.cin - c.c_split) % 64 == 0) ? 64 : 32;      // a K-chunk never straddles the two inputs
         c.enc_n = 0;
         c.halo = halo_config(c, c.halo_bn, c.halo_stages);
         c.halo_maps = false;
@@ -837,6 +847,7 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
         memset(&p, 0, sizeof(p));
         p.N = N; p.H = c.Hout; p.W = c.Wout; p.Cout = c.cout; p.n_base = 0;
         p.cin_chunks = c.cin / c.kc;
+        p.split_chunks = c.c_split / c.kc;
         p.tiles_x = ceil_div(c.Wout, 8); p.tiles_y = ceil_div(c.Hout, 16);
         p.n_stages = c.halo_stages;
         p.out_ps = c.cout; p.out = c.out_raw; p.bias = c.b.dev; p.stats = c.stats;
@@ -848,13 +859,15 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
             p.in_eps = pl.eps; p.in_slope = pl.negative_slope;
         }
         if (c.first || !c.halo_maps) {
-            if ((rc = encode_act_map(&c.tmA, c.in, c.in_ps, c.cin, c.Hin, c.Win, pl.max_batch, 0, c.kc, kHaloW, kHaloH, 1, es, is_bf16))) return rc;
+            if ((rc = encode_act_map(&c.tmA, c.in, c.in_ps, c.c_split, c.Hin, c.Win, pl.max_batch, 0, c.kc, kHaloW, kHaloH, 1, es, is_bf16))) return rc;
+            if (c.in2) { if ((rc = encode_act_map(&c.tmA2, c.in2, c.in2_ps, c.cin - c.c_split, c.Hin, c.Win, pl.max_batch, 0, c.kc, kHaloW, kHaloH, 1, es, is_bf16))) return rc; }
+            else c.tmA2 = c.tmA;
             if ((rc = encode_w_map(&c.tmB, c.w_tc, c.cin, c.cout, 9, c.kc, c.halo_bn, es, is_bf16))) return rc;
             c.halo_maps = true;
         }
         const int smem = halo_smem_bytes(c.cin, c.halo_bn, c.kc, c.halo_stages);
-        rc = is_bf16 ? launch_halo<__nv_bfloat16>(c.halo_bn, c.kc, fuse, c.tmA, c.tmB, p, smem, st)
-                     : launch_halo<__half>(c.halo_bn, c.kc, fuse, c.tmA, c.tmB, p, smem, st);
+        rc = is_bf16 ? launch_halo<__nv_bfloat16>(c.halo_bn, c.kc, fuse, c.tmA, c.tmA2, c.tmB, p, smem, st)
+                     : launch_halo<__half>(c.halo_bn, c.kc, fuse, c.tmA, c.tmA2, c.tmB, p, smem, st);
         if (rc) return rc;
     } else if (c.tc) {
         ConvTcParams p;
@@ -879,12 +892,15 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
         fill_tc_params(p, N, c.Hout, c.Wout, c.cout, c.cin, c.kc, bn, c.kh * c.kw, c.kw, (c.kh - 1) / 2, (c.kw - 1) / 2, s2, c.in_ps);
         p.tw = tw; p.th = th; p.tn = tn;
         p.tiles_w = ceil_div(c.Wout, tw); p.tiles_h = ceil_div(c.Hout, th); p.tiles_n = ceil_div(N, tn);
+        p.split_chunks = c.c_split / c.kc;
         p.out_ps = c.cout; p.out = c.out_raw; p.bias = c.b.dev; p.stats = c.stats;
         if (ksplit >= 1) { p.ksplit = ksplit; p.partial = u->partial; p.stats = nullptr; p.bias = nullptr; }
         p.mc = (mc_on && ksplit == 0 && m_tiles % 2 == 0 && bn >= 32) ? 1 : 0;
         // descriptors depend on (input pointer, batch-dependent tile box, BN): cache by (N, bn)
         if (c.first || c.bn != bn * (p.mc ? -1 : 1) || c.enc_n != N) {
-            if ((rc = encode_act_map(&c.tmA, c.in, c.in_ps, c.cin, c.Hin, c.Win, pl.max_batch, s2, c.kc, tw, th, tn, es, is_bf16))) return rc;
+            if ((rc = encode_act_map(&c.tmA, c.in, c.in_ps, c.c_split, c.Hin, c.Win, pl.max_batch, s2, c.kc, tw, th, tn, es, is_bf16))) return rc;
+            if (c.in2) { if ((rc = encode_act_map(&c.tmA2, c.in2, c.in2_ps, c.cin - c.c_split, c.Hin, c.Win, pl.max_batch, s2, c.kc, tw, th, tn, es, is_bf16))) return rc; }
+            else c.tmA2 = c.tmA;
             if ((rc = encode_w_map(&c.tmB, c.w_tc, c.cin, c.cout, c.kh * c.kw, c.kc, p.mc ? bn / 2 : bn, es, is_bf16))) return rc;
             c.bn = bn * (p.mc ? -1 : 1);       // cache key: (BN, multicast or not)
             c.enc_n = N;
@@ -892,7 +908,7 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
         static long long *tc_dbg = nullptr;
         static const int tc_dbg_on = env_int("TS2D_TC_DBG", 0);
         for (int rep = 1; rep < tc_dbg_on; ++rep) {      // TS2D_TC_DBG = 2: every launch twice (the second finds its weights in L2)
-            rc = is_bf16 ? launch_tc<__nv_bfloat16>(bn, c.kc, c.tmA, c.tmB, p, st) : launch_tc<__half>(bn, c.kc, c.tmA, c.tmB, p, st);
+            rc = is_bf16 ? launch_tc<__nv_bfloat16>(bn, c.kc, c.tmA, c.tmA2, c.tmB, p, st) : launch_tc<__half>(bn, c.kc, c.tmA, c.tmA2, c.tmB, p, st);
             if (rc) return rc;
         }
         if (tc_dbg_on) {
@@ -900,8 +916,8 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
             TS2D_CHECK_CUDA(cudaMemsetAsync(tc_dbg, 0, kNumSMs * 8 * sizeof(long long), st));
             p.dbg = tc_dbg;
         }
-        if (bn2) rc = is_bf16 ? launch_tc2<__nv_bfloat16>(bn, c.tmA, c.tmB, p, st) : launch_tc2<__half>(bn, c.tmA, c.tmB, p, st);
-        else rc = is_bf16 ? launch_tc<__nv_bfloat16>(bn, c.kc, c.tmA, c.tmB, p, st) : launch_tc<__half>(bn, c.kc, c.tmA, c.tmB, p, st);
+        if (bn2) rc = is_bf16 ? launch_tc2<__nv_bfloat16>(bn, c.tmA, c.tmA2, c.tmB, p, st) : launch_tc2<__half>(bn, c.tmA, c.tmA2, c.tmB, p, st);
+        else rc = is_bf16 ? launch_tc<__nv_bfloat16>(bn, c.kc, c.tmA, c.tmA2, c.tmB, p, st) : launch_tc<__half>(bn, c.kc, c.tmA, c.tmA2, c.tmB, p, st);
         if (rc) return rc;
         if (tc_dbg_on) {
             // clock stamps (cycles since the CTA started): prologue, first loads issued, all loads issued, first operands landed,
@@ -951,6 +967,7 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
         DirectConvParams p;
         memset(&p, 0, sizeof(p));
         p.in = c.in; p.in_ps = c.in_ps; p.Hin = c.Hin; p.Win = c.Win; p.Cin = c.cin;
+        p.in2 = c.in2; p.in2_ps = c.in2_ps; p.c_split = c.c_split;
         p.w = c.w_direct; p.bias = c.b.dev;
         p.out = c.out_raw; p.out_ps = c.cout; p.Hout = c.Hout; p.Wout = c.Wout; p.Cout = c.cout;
         p.kh = c.kh; p.kw = c.kw; p.sh = c.sh; p.sw = c.sw; p.ph = (c.kh - 1) / 2; p.pw = (c.kw - 1) / 2;
@@ -1013,7 +1030,7 @@ static int run_up(ts2d_unet *u, UpLayer &up, int N, cudaStream_t st) {
             up.bn = bn * (p.mc ? -1 : 1);
             up.enc_n = N;
         }
-        rc = is_bf16 ? launch_tc<__nv_bfloat16>(bn, up.kc, up.tmA, up.tmB, p, st) : launch_tc<__half>(bn, up.kc, up.tmA, up.tmB, p, st);
+        rc = is_bf16 ? launch_tc<__nv_bfloat16>(bn, up.kc, up.tmA, up.tmA, up.tmB, p, st) : launch_tc<__half>(bn, up.kc, up.tmA, up.tmA, up.tmB, p, st);
         if (rc) return rc;
         u->launches++;
     } else {
@@ -1021,7 +1038,7 @@ static int run_up(ts2d_unet *u, UpLayer &up, int N, cudaStream_t st) {
             for (int dx = 0; dx < up.sw; ++dx) {
                 DirectConvParams p;
                 memset(&p, 0, sizeof(p));
-                p.in = up.in; p.in_ps = up.cin; p.Hin = up.Hin; p.Win = up.Win; p.Cin = up.cin;
+                p.in = up.in; p.in_ps = up.cin; p.Hin = up.Hin; p.Win = up.Win; p.Cin = up.cin; p.c_split = up.cin;
                 p.w = up.w_direct + (size_t)(dy * up.sw + dx) * up.cin * up.cout; p.bias = up.b.dev;
                 p.out = up.out; p.out_ps = up.out_ps; p.Hout = up.Hin; p.Wout = up.Win; p.Cout = up.cout;
                 p.kh = 1; p.kw = 1; p.sh = 1; p.sw = 1; p.ph = 0; p.pw = 0;

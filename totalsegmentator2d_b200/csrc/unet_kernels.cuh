@@ -18,6 +18,7 @@ namespace ts2d {
 // ------------------------------------------------------------------------------------------------------
 struct DirectConvParams {
     const void *in; long long in_ps; int Hin, Win, Cin;
+    const void *in2; long long in2_ps; int c_split;     // channels [c_split, Cin) come from in2 (decoder convs: up-sampled tensor + skip); c_split == Cin: one input
     const float *w; const float *bias;
     void *out; long long out_ps; int Hout, Wout, Cout;
     int kh, kw, sh, sw, ph, pw;
@@ -33,6 +34,7 @@ __global__ void __launch_bounds__(128) conv_direct_kernel(const DirectConvParams
     const int co0 = blockIdx.y * 32 + warp * 8;
     const int npix = p.Hout * p.Wout;
     const T *in = reinterpret_cast<const T *>(p.in) + (long long)n * p.Hin * p.Win * p.in_ps;
+    const T *in2 = p.in2 ? reinterpret_cast<const T *>(p.in2) + (long long)n * p.Hin * p.Win * p.in2_ps : in;
     T *out = reinterpret_cast<T *>(p.out);
     float ssum[8], ssq[8];
 #pragma unroll
@@ -51,9 +53,10 @@ __global__ void __launch_bounds__(128) conv_direct_kernel(const DirectConvParams
                     const int ix = ox * p.sw + s - p.pw;
                     const bool inb = valid && iy >= 0 && iy < p.Hin && ix >= 0 && ix < p.Win;
                     const T *ip = in + ((long long)iy * p.Win + ix) * p.in_ps;
+                    const T *ip2 = in2 + ((long long)iy * p.Win + ix) * p.in2_ps - p.c_split;
                     const float *wp = p.w + (long long)(r * p.kw + s) * p.Cin * p.Cout + co0;
                     for (int ci = 0; ci < p.Cin; ++ci) {
-                        const float x = inb ? to_f32<T>(ip[ci]) : 0.f;
+                        const float x = inb ? to_f32<T>(ci < p.c_split ? ip[ci] : ip2[ci]) : 0.f;
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
                             const float wv = (co0 + j < p.Cout) ? __ldg(wp + (long long)ci * p.Cout + j) : 0.f;
