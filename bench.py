@@ -251,7 +251,7 @@ def run_reference(args):
 
 def config_dict(args, shape, patch, studies_per_step):
     return {"workload": "ts2d-v2 5-model pipeline, synthetic CT {}x{}x{} int16 1.5mm, CS-{} plan, 117 labels".format(shape[2], shape[1], shape[0], patch[0]),
-            "studies_per_step_per_gpu": studies_per_step, "orientations": "study i: i%8==3 x/y swapped + flips, i%8==7 y/z swapped + flips, else RAI",
+            "studies_per_step_per_gpu": studies_per_step, "orientations": "study j of a rank: j%8==3 x/y swapped + flips, j%8==7 y/z swapped + flips, else RAI (1 in 4 at 4 studies per step)",
             "tile_step_size": 0.5, "mirror_tta": bool(args.mirror), "models": 5,
             "parallelism": "studies sharded over GPUs, no collective", "l2": "inputs larger than L2 (524 MB per study)",
             "small": bool(args.small)}
@@ -321,7 +321,9 @@ def run_b200(args):
     host_vols, dirs = [], []
     from totalsegmentator2d_b200 import shard
     for i in shard.shard_indices(S * world, rank, world):      # study i -> rank i mod world
-        d, shp = study_orientation(i, shape)
+        # orientation by the study's LOCAL index j = i // world: every rank gets the same mix as the single-GPU run (weak scaling);
+        # keyed on i itself, rank 3 and rank 7 of an 8-rank run would hold only permuted volumes
+        d, shp = study_orientation(i // world, shape)
         v = torch.from_numpy(synthetic_volume(20260000 + i, shp)).pin_memory()
         host_vols.append(v)
         dirs.append(d)
@@ -407,8 +409,10 @@ def run_b200(args):
     reps = 10
     pms = []
     ident = [k for k in range(S) if np.array_equal(dirs[k], np.eye(3))]      # the RAI-stored studies (reduce over n1)
+    if not ident:       # (cannot happen with the local-index orientation rule and S >= 1; kept so that the probe never divides by zero)
+        ident_vol = torch.from_numpy(synthetic_volume(20260000, shape)).cuda()
     for r in range(reps):
-        v = dev_vols[ident[r % len(ident)]]
+        v = dev_vols[ident[r % len(ident)]] if ident else ident_vol
         pe0.record()
         ops.project(v, ["mean", "max"], reduce_dim=1, h_dim=0, out=out)
         pe1.record()
