@@ -178,6 +178,11 @@ int64_t ts2d_unet_launch_count(const ts2d_unet *u);
  * strides other than 1 / 2 per axis).  ts2d_unet_finalize logs each such layer to stderr once; 0 for every nnU-Net 2-D plan tested
  * (reference plans come from nnunetv2ml's planner: ts2d/core/inference/nnu.py:149-166). */
 int ts2d_unet_direct_layer_count(const ts2d_unet *u);
+/* debug aid (compute-sanitizer is not available on every GPU pool): with TS2D_ARENA_GUARD=<bytes> in the environment at
+ * ts2d_unet_finalize time every workspace buffer is followed by a canary band; returns the number of damaged bands (0 = no kernel
+ * stored outside its buffer), the number of bands being 0 when the variable is unset; -1 on a CUDA error. Synchronises the device. */
+int ts2d_unet_check_guards(ts2d_unet *u);
+int ts2d_unet_guard_count(const ts2d_unet *u);
 /* conv/transposed-conv/head FLOPs (MAC = 2) of one forward at `batch` images */
 double ts2d_unet_flops(const ts2d_unet *u, int batch);
 /* device time (ms) the conv kernels of the last forward took; needs ts2d_unet_set_profiling(u, 1) */

@@ -155,6 +155,41 @@ def test_sliding_window_logits_and_mask(precision, tol, mirror):
         assert agree >= 0.999
 
 
+@pytest.mark.parametrize("precision", ["fp16", "bf16", "fp32"])
+def test_no_kernel_stores_outside_its_buffer(precision, monkeypatch):
+    """Stand-in for compute-sanitizer memcheck (closed on the GPU pool): with TS2D_ARENA_GUARD every workspace buffer of the engine
+    is followed by a 64 KiB canary band; after forwards that exercise every conv kernel (first-layer tcgen05, halo + fused transform,
+    conv_tc with ragged / multi-image tiles and split-K, conv_tc2, anisotropic strides and 2-tap transposed convs, the CUDA-core
+    kernels in fp32) on shapes whose tiles overhang the image, no band may be damaged.  Outputs handed in by the caller (logits, mask)
+    get their own canaries."""
+    monkeypatch.setenv("TS2D_ARENA_GUARD", "65536")
+    monkeypatch.setenv("TS2D_TC2_MIN_UNITS", "1")
+    dt = {"fp16": torch.float16, "bf16": torch.bfloat16, "fp32": torch.float32}[precision]
+    cases = [([32, 32, 64, 64, 64], (48, 160), None), ([32, 64, 128, 256, 256], (80, 96), None),
+             ([32, 64, 128, 128], (80, 48), [[1, 1], [2, 2], [2, 1], [1, 2]])]
+    if precision == "fp32":
+        cases = [([8, 16, 32], (40, 72), None), ([8, 16, 16], (24, 40), [[1, 1], [2, 2], [2, 1]])]
+    for feats, patch, strides in cases:
+        p, sd, spec = _make(feats, patch, heads=5, precision=precision, seed=3, strides=strides)
+        x, xd = _tiles(3, 2, patch, 7, dt)
+        logits = p.predict_tile_logits(xd)
+        n, bad = p.check_guards()
+        assert n > 0 and bad == 0, (feats, patch, n, bad)
+        # blend + head + mask export into canary-framed outputs
+        g = torch.Generator().manual_seed(5)
+        data = torch.randn(2, patch[0] + 21, patch[1] + 13, generator=g).cuda()
+        tiles, layout = p.make_tiles(data)
+        h, w = data.shape[1:]
+        buf = torch.full((h + 4, w, 9), 0x5A, dtype=torch.uint8, device="cuda")
+        p.run_tiles(tiles, layout, (h, w), mask=buf[2:-2], crop_origin=(0, 0), ch_off=2)
+        assert int((buf[:2] != 0x5A).sum()) == 0 and int((buf[-2:] != 0x5A).sum()) == 0
+        assert int((buf[2:-2, :, :2] != 0x5A).sum()) == 0 and int((buf[2:-2, :, 7:] != 0x5A).sum()) == 0
+        n, bad = p.check_guards()
+        assert bad == 0, (feats, patch, n, bad)
+        assert torch.isfinite(logits).all()
+        p.close()
+
+
 def test_errors_are_loud():
     from totalsegmentator2d_b200 import _lib as L
     p, sd, spec = _make([8, 16], (16, 16))

@@ -82,6 +82,8 @@ _PROTOS = {
     "ts2d_merge_present_order": (_i, [_vp, _vp, _i64, _i, _vp, _ip, _i, _vp, _vp]),
     "ts2d_unet_launch_count": (_i64, [_vp]),
     "ts2d_unet_direct_layer_count": (_i, [_vp]),
+    "ts2d_unet_check_guards": (_i, [_vp]),
+    "ts2d_unet_guard_count": (_i, [_vp]),
     "ts2d_unet_blend_covers_image": (_i, [_vp]),
     "ts2d_unet_flops": (C.c_double, [_vp, _i]),
     "ts2d_unet_set_profiling": (_i, [_vp, _i]),

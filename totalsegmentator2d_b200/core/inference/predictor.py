@@ -209,6 +209,14 @@ class B200nnUNetPredictor:
         """layers of a reduced-precision tensor-core plan that run on the CUDA-core parity kernel (0 = every conv is on tcgen05)"""
         return sum(int(self._lib.ts2d_unet_direct_layer_count(h)) for h in self._handles)
 
+    def check_guards(self):
+        """(canary bands, damaged bands) of the engines' workspaces; bands exist when TS2D_ARENA_GUARD was set at initialisation"""
+        n = sum(int(self._lib.ts2d_unet_guard_count(h)) for h in self._handles)
+        bad = [int(self._lib.ts2d_unet_check_guards(h)) for h in self._handles]
+        if any(b < 0 for b in bad):
+            raise L.TS2DError("ts2d_unet_check_guards failed (CUDA error)")
+        return n, sum(bad)
+
     def flops(self, batch: int) -> float:
         return float(self._lib.ts2d_unet_flops(self._handles[0], batch)) * len(self._handles)
 

@@ -121,6 +121,7 @@ struct ts2d_unet {
     void *features = nullptr;     // last decoder output [N][P][P][C0]
     int last_batch = 0;
     long long launches = 0;
+    std::vector<std::pair<size_t, size_t>> guards;   // TS2D_ARENA_GUARD=bytes: (offset, bytes) of the canary bands between the workspace buffers
     int direct_layers = 0;        // layers of a reduced-precision tensor-core plan that fell to conv_direct_kernel (logged at finalize)
     bool profiling = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
@@ -645,8 +646,16 @@ extern "C" int ts2d_unet_finalize(ts2d_unet *u) {
     if (prop.major != 10) { set_error("ts2d_unet_finalize: device %d is sm_%d%d, this library contains sm_100a code only", dev, prop.major, prop.minor); return TS2D_ERR_DEVICE; }
 
     // ---- workspace ----
-    auto align = [](size_t v) { return (v + 1023) & ~(size_t)1023; };
+    // TS2D_ARENA_GUARD=n (debug; compute-sanitizer is not available on the GPU pool): n bytes of 0xA5 after every workspace buffer,
+    // verified by ts2d_unet_check_guards() - an out-of-bounds store of any kernel into a neighbouring buffer shows up as a damaged band
+    const size_t guard = ((size_t)std::max(0, env_int("TS2D_ARENA_GUARD", 0)) + 1023) & ~(size_t)1023;
+    u->guards.clear();
     size_t off = 0;
+    auto align = [&](size_t v) {
+        const size_t a = (v + 1023) & ~(size_t)1023;
+        if (guard) u->guards.push_back({off + a, guard});
+        return a + guard;
+    };
     std::vector<size_t> skip_off(L - 1), up_off(L - 1);
     for (int l = 0; l < L - 1; ++l) {
         skip_off[l] = off; off += align((size_t)N * u->H[l] * u->W[l] * u->C[l] * es);
@@ -666,11 +675,14 @@ extern "C" int ts2d_unet_finalize(ts2d_unet *u) {
     const size_t partial_off = off; off += align(max_partial);
     const size_t stats_off = off;
     size_t sbytes = 0;
-    for (auto &c : u->convs) sbytes += align((size_t)N * c.cout * 2 * sizeof(double));
+    auto align0 = [](size_t v) { return (v + 1023) & ~(size_t)1023; };      // the statistics block is one buffer (cleared by one memset per forward): no bands inside
+    for (auto &c : u->convs) sbytes += align0((size_t)N * c.cout * 2 * sizeof(double));
     off += sbytes;
+    if (guard) { u->guards.push_back({off, guard}); off += guard; }
     if (u->arena) cudaFree(u->arena);
     TS2D_CHECK_CUDA(cudaMalloc(&u->arena, off));
     TS2D_CHECK_CUDA(cudaMemset(u->arena, 0, off));
+    for (auto &g : u->guards) TS2D_CHECK_CUDA(cudaMemset(u->arena + g.first, 0xA5, g.second));
     u->arena_bytes = off;
     u->skip.resize(L - 1); u->up.resize(L - 1);
     for (int l = 0; l < L - 1; ++l) { u->skip[l] = u->arena + skip_off[l]; u->up[l] = u->arena + up_off[l]; }
@@ -681,7 +693,7 @@ extern "C" int ts2d_unet_finalize(ts2d_unet *u) {
     u->stats_arena = reinterpret_cast<double *>(u->arena + stats_off);
     u->stats_bytes = sbytes;
     size_t so = 0;
-    for (auto &c : u->convs) { c.stats = reinterpret_cast<double *>(u->arena + stats_off + so); so += align((size_t)N * c.cout * 2 * sizeof(double)); }
+    for (auto &c : u->convs) { c.stats = reinterpret_cast<double *>(u->arena + stats_off + so); so += align0((size_t)N * c.cout * 2 * sizeof(double)); }
 
     // ---- wiring ----
     size_t ci = 0;
@@ -787,6 +799,20 @@ extern "C" int ts2d_unet_finalize(ts2d_unet *u) {
 
 extern "C" size_t ts2d_unet_workspace_bytes(const ts2d_unet *u) { return u ? u->arena_bytes : 0; }
 extern "C" int64_t ts2d_unet_launch_count(const ts2d_unet *u) { return u ? u->launches : 0; }
+extern "C" int ts2d_unet_guard_count(const ts2d_unet *u) { return u ? (int)u->guards.size() : 0; }
+extern "C" int ts2d_unet_check_guards(ts2d_unet *u) {
+    if (!u || !u->arena) return -1;
+    if (cudaDeviceSynchronize() != cudaSuccess) return -1;
+    int bad = 0;
+    std::vector<uint8_t> h;
+    for (auto &g : u->guards) {
+        h.resize(g.second);
+        if (cudaMemcpy(h.data(), u->arena + g.first, g.second, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+        for (size_t i = 0; i < g.second; ++i)
+            if (h[i] != 0xA5) { ++bad; fprintf(stderr, "[ts2d] guard band at workspace offset %zu damaged at byte %zu\n", g.first, i); break; }
+    }
+    return bad;
+}
 extern "C" int ts2d_unet_direct_layer_count(const ts2d_unet *u) { return u ? u->direct_layers : 0; }
 
 extern "C" double ts2d_unet_flops(const ts2d_unet *u, int batch) {
