@@ -190,6 +190,35 @@ def test_no_kernel_stores_outside_its_buffer(precision, monkeypatch):
         p.close()
 
 
+@pytest.mark.parametrize("precision", ["fp16", "bf16"])
+@pytest.mark.parametrize("feats,patch", [([32, 64, 128], (96, 80)), ([64, 64, 64], (72, 104)), ([32, 32, 64], (64, 48))])
+def test_stride2_halo_kernel(precision, feats, patch, monkeypatch):
+    """conv_halo_s2_kernel (four parity-plane halos per tile, taps as shifted descriptors, resident weights) against conv_tc_kernel on the
+    same strided layer (TS2D_CONV_HALO_S2=0): with one K-chunk per tap both accumulate the same products in the same order, so the conv
+    outputs agree bit for bit wherever the InstanceNorm statistics (grouped differently) round alike; and against the fp32 oracle.
+    Patches whose 8 x 16 output tiles overhang the image, 32 / 64 input channels (KC = 32 / 64), 32 / 64 output channels."""
+    dt = torch.bfloat16 if precision == "bf16" else torch.float16
+    outs = {}
+    for s2 in ("1", "0"):
+        monkeypatch.setenv("TS2D_CONV_HALO_S2", s2)
+        p, sd, spec = _make(feats, patch, heads=4, precision=precision, seed=29)
+        x, xd = _tiles(3, 2, patch, 8, dt)
+        x = xd.float().cpu().permute(0, 3, 1, 2).contiguous()
+        coll = {}
+        with torch.no_grad():
+            nnunet_net.unet_forward(x, sd, spec, collect=coll)
+        outs[s2] = {n: p.forward_debug(xd, n, tuple(coll[n].shape[1:])).cpu() for n in ("enc1.0", "enc1.1", "enc2.0")}
+        if s2 == "1":
+            errs = {n: float((outs[s2][n] - coll[n]).abs().max()) for n in outs[s2]}
+            assert max(errs.values()) <= (0.15 if precision == "bf16" else 0.02), errs
+        p.close()
+    ulp = 2.0 ** -5 if precision == "bf16" else 2.0 ** -8
+    d = (outs["1"]["enc1.0"] - outs["0"]["enc1.0"]).abs()
+    assert float(d.max()) <= ulp and float((d == 0).float().mean()) >= 0.98, (float(d.max()), float((d == 0).float().mean()))
+    for n in ("enc1.1", "enc2.0"):
+        assert float((outs["1"][n] - outs["0"][n]).abs().max()) <= 2 * ulp
+
+
 def test_errors_are_loud():
     from totalsegmentator2d_b200 import _lib as L
     p, sd, spec = _make([8, 16], (16, 16))

@@ -49,6 +49,7 @@ struct ConvHaloParams {
     int tiles_x, tiles_y;       // ceil(W/8), ceil(H/16)
     int n_stages;               // halo ring depth (host: what fits beside the resident weights)
     long long out_ps;           // output pixel stride in elements
+    int in_ps;                  // conv_halo_s2_kernel: input pixel stride in elements (selects the odd column of the parity view)
     void *out;
     const float *bias;          // [Cout] or null
     double *stats;              // [Nmax][Cout][2] or null  (sum, sum of squares of the ROUNDED outputs)

@@ -22,6 +22,7 @@
 #include "conv_tc.cuh"
 #include "conv_tc2.cuh"
 #include "conv_halo.cuh"
+#include "conv_halo_s2.cuh"
 #include "conv_first_tc.cuh"
 #include "unet_kernels.cuh"
 #include "blend.cuh"
@@ -70,6 +71,7 @@ struct ConvLayer {
     bool halo = false;          // conv_halo_kernel (3x3 stride 1, halo tile + resident weights)
     int halo_bn = 0, halo_stages = 0;
     bool halo_maps = false;
+    bool halo_s2 = false;       // conv_halo_s2_kernel (3x3 stride 2, parity-plane halo + resident weights)
     bool first_tc = false;      // conv_first_tc_kernel (CIN == 2, 3x3 stride 1: im2col rows built by the workers, K = 32)
     bool first_fast = false;    // conv_first_kernel (CIN <= 4, 3x3 stride 1, 16-bit activations)
     void *out_raw = nullptr;    // pre-normalisation output (ping-pong between two buffers)
@@ -362,6 +364,53 @@ static int launch_halo(int bn, int kc, bool fuse, const CUtensorMap &tmA, const 
 #undef TS2D_HALO_CASE
     set_error("no halo conv instantiation for BN=%d KC=%d", bn, kc);
     return TS2D_ERR_UNSUPPORTED;
+}
+
+static int halo_s2_smem_bytes(int cin, int bn, int kc, int stages) {
+    const int w = ((9 * cin * bn * 2) + 1023) & ~1023;
+    const int st = kc == 64 ? s2_stage_bytes<64>() : s2_stage_bytes<32>();
+    return 1024 /*align*/ + w + stages * st + kHaloTailBytes;
+}
+template <int BN, int KC, typename DT>
+static int launch_halo_s2_inst(const CUtensorMap &tmA, const CUtensorMap &tmB, const ConvHaloParams &p, int smem, cudaStream_t st) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        TS2D_CHECK_CUDA(cudaFuncSetAttribute(conv_halo_s2_kernel<BN, KC, DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHaloSmemBudget));
+        attr_set = true;
+    }
+    const int n_tiles_n = p.Cout / BN;
+    const int total = p.tiles_x * p.tiles_y * p.N;
+    const int gx = std::max(1, std::min(total, kNumSMs / n_tiles_n));
+    TS2D_CHECK_CUDA(launch_pdl(conv_halo_s2_kernel<BN, KC, DT>, dim3(gx, n_tiles_n), dim3(384), smem, st, tmA, tmB, p));
+    TS2D_LAUNCH_CHECK();
+    return TS2D_OK;
+}
+template <typename DT>
+static int launch_halo_s2(int bn, int kc, const CUtensorMap &tmA, const CUtensorMap &tmB, const ConvHaloParams &p, int smem, cudaStream_t st) {
+    if (bn == 32 && kc == 32) return launch_halo_s2_inst<32, 32, DT>(tmA, tmB, p, smem, st);
+    if (bn == 64 && kc == 32) return launch_halo_s2_inst<64, 32, DT>(tmA, tmB, p, smem, st);
+    if (bn == 32 && kc == 64) return launch_halo_s2_inst<32, 64, DT>(tmA, tmB, p, smem, st);
+    if (bn == 64 && kc == 64) return launch_halo_s2_inst<64, 64, DT>(tmA, tmB, p, smem, st);
+    set_error("no stride-2 halo conv instantiation for BN=%d KC=%d", bn, kc);
+    return TS2D_ERR_UNSUPPORTED;
+}
+// stride-2 halo kernel: the strided convs whose parity-plane halos (4 x 9 x 17 pixels per K-chunk) and resident weights fit in shared
+// memory with >= 2 ring stages - the first strided stage of a plan (enc1.0 of CS-512: 32 -> 64 channels); deeper ones use conv_tc / tc2
+static bool halo_s2_config(const ConvLayer &c, int &bn, int &stages) {
+    const int enable = env_int("TS2D_CONV_HALO_S2", 1), max_nt = env_int("TS2D_HALO_MAX_NT", 2);
+    if (!enable || !c.tc || c.kh != 3 || c.kw != 3 || c.sh != 2 || c.sw != 2 || c.in2) return false;
+    if (c.Hout < 16 || c.Wout < 8) return false;
+    const double covered = (double)ceil_div(c.Wout, 8) * 8 * ceil_div(c.Hout, 16) * 16;
+    if (covered > 1.3 * c.Wout * c.Hout) return false;
+    for (int b : {64, 32}) {
+        if (c.cout % b || c.cout / b > max_nt) continue;
+        int st = 6;
+        while (st >= 2 && halo_s2_smem_bytes(c.cin, b, c.kc, st) > kHaloSmemBudget) --st;
+        if (st < 2) continue;
+        bn = b; stages = st;
+        return true;
+    }
+    return false;
 }
 
 // picks the output-channel block and ring depth of the halo kernel, or returns false when the layer should use conv_tc_kernel
@@ -737,6 +786,7 @@ extern "C" int ts2d_unet_finalize(ts2d_unet *u) {
         if (c.tc) c.kc = (c.c_split % 64 == 0 && (c.cin - c.c_split) % 64 == 0) ? 64 : 32;      // a K-chunk never straddles the two inputs
         c.enc_n = 0;
         c.halo = halo_config(c, c.halo_bn, c.halo_stages);
+        c.halo_s2 = !c.halo && halo_s2_config(c, c.halo_bn, c.halo_stages);
         c.halo_maps = false;
         c.first_tc = !c.tc && first_tc_eligible(pl, c);
         c.first_fast = !c.tc && !c.first_tc && first_fast_eligible(pl, c);
@@ -868,7 +918,25 @@ static int run_conv(ts2d_unet *u, ConvLayer &c, int N, cudaStream_t st) {
     const bool is_bf16 = pl.precision == TS2D_PREC_BF16;
     int rc;
     if ((rc = prof_begin(u, st))) return rc;
-    if (c.halo) {
+    if (c.halo_s2) {
+        ConvHaloParams p;
+        memset(&p, 0, sizeof(p));
+        p.N = N; p.H = c.Hout; p.W = c.Wout; p.Cout = c.cout; p.n_base = 0;
+        p.cin_chunks = c.cin / c.kc; p.split_chunks = p.cin_chunks;
+        p.tiles_x = ceil_div(c.Wout, 8); p.tiles_y = ceil_div(c.Hout, 16);
+        p.n_stages = c.halo_stages;
+        p.out_ps = c.cout; p.in_ps = (int)c.in_ps; p.out = c.out_raw; p.bias = c.b.dev; p.stats = c.stats;
+        p.Cin = c.cin;
+        if (c.first || !c.halo_maps) {
+            if ((rc = encode_act_map(&c.tmA, c.in, c.in_ps, c.cin, c.Hin, c.Win, pl.max_batch, 3, c.kc, kS2W, kS2H, 1, es, is_bf16))) return rc;
+            if ((rc = encode_w_map(&c.tmB, c.w_tc, c.cin, c.cout, 9, c.kc, c.halo_bn, es, is_bf16))) return rc;
+            c.halo_maps = true;
+        }
+        const int smem = halo_s2_smem_bytes(c.cin, c.halo_bn, c.kc, c.halo_stages);
+        rc = is_bf16 ? launch_halo_s2<__nv_bfloat16>(c.halo_bn, c.kc, c.tmA, c.tmB, p, smem, st)
+                     : launch_halo_s2<__half>(c.halo_bn, c.kc, c.tmA, c.tmB, p, smem, st);
+        if (rc) return rc;
+    } else if (c.halo) {
         ConvHaloParams p;
         memset(&p, 0, sizeof(p));
         p.N = N; p.H = c.Hout; p.W = c.Wout; p.Cout = c.cout; p.n_base = 0;
