@@ -130,6 +130,27 @@ __device__ __forceinline__ void tma_load_5d(void *dst, const CUtensorMap *tm, ui
     asm volatile("cp.async.bulk.tensor.5d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
                  ::"r"(smem_u32(dst)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4) : "memory");
 }
+// ---- warp-uniform TMA issue (same reason as the warp-uniform MMA issue below) ----
+// The producer warp runs its loop CONVERGENTLY: all 32 lanes compute the (uniform) coordinates, which then live in uniform registers, and
+// only the copy itself is predicated on one elected lane.  Issued from inside `if (lane == 0)` every operand is a per-thread value and each
+// UTMALDG costs an ELECT + 6 x R2UR.BROADCAST "waterfall" loop; measured on conv_tc2_kernel, whose k-chunks are bound by how fast the
+// producer can issue: 256 -> 256 channels at 64^2 0.064 -> 0.056 ms for one extra branch in that loop (profiles/r02t_layers_exp.txt).
+__device__ __forceinline__ void mbar_expect_tx_pred(uint32_t leader, uint64_t *bar, uint32_t bytes) {
+    asm volatile("{\n.reg .pred q;\nsetp.ne.b32 q, %0, 0;\n@q mbarrier.arrive.expect_tx.shared::cta.b64 _, [%1], %2;\n}" ::"r"(leader), "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d_pred(uint32_t leader, uint32_t dst, const CUtensorMap *tm, uint64_t *bar, int c0, int c1, int c2) {
+    asm volatile("{\n.reg .pred q;\nsetp.ne.b32 q, %0, 0;\n@q cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%1], [%2, {%4, %5, %6}], [%3];\n}"
+                 ::"r"(leader), "r"(dst), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+__device__ __forceinline__ void tma_load_4d_pred(uint32_t leader, uint32_t dst, const CUtensorMap *tm, uint64_t *bar, int c0, int c1, int c2, int c3) {
+    asm volatile("{\n.reg .pred q;\nsetp.ne.b32 q, %0, 0;\n@q cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%1], [%2, {%4, %5, %6, %7}], [%3];\n}"
+                 ::"r"(leader), "r"(dst), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+__device__ __forceinline__ void tma_load_5d_pred(uint32_t leader, uint32_t dst, const CUtensorMap *tm, uint64_t *bar, int c0, int c1, int c2, int c3, int c4) {
+    asm volatile("{\n.reg .pred q;\nsetp.ne.b32 q, %0, 0;\n@q cp.async.bulk.tensor.5d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%1], [%2, {%4, %5, %6, %7, %8}], [%3];\n}"
+                 ::"r"(leader), "r"(dst), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4) : "memory");
+}
+__device__ __forceinline__ uint32_t elect_one();
 __device__ __forceinline__ void tma_load_3d_mc(void *dst, const CUtensorMap *tm, uint64_t *bar, int c0, int c1, int c2, uint16_t mask) {
     asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4, %5}], [%2], %6;"
                  ::"r"(smem_u32(dst)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "h"(mask) : "memory");
@@ -391,40 +412,44 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int t_end = (int)((long long)total_tiles * (part + 1) / nparts);
 
     if (warp == 0) {
-        // ===================== TMA producer =====================
-        if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int tile = t_begin; tile < t_end; ++tile) {
-                const int ot = tile / ksplit, ks = tile - ot * ksplit;      // (output tile, K slice), slice fastest
-                const int nt = ot / mseq, mt = (ot - nt * mseq) * mstep + (int)rank;
-                const int xt = mt % p.tiles_w, yt = (mt / p.tiles_w) % p.tiles_h, nn = mt / (p.tiles_w * p.tiles_h);
-                const int x0 = xt * p.tw, y0 = yt * p.th, n0 = nn * p.tn;
-                for (int kc = ks * k_per; kc < (ks + 1) * k_per; ++kc) {
-                    const int tap = kc / p.cin_chunks, cc = kc % p.cin_chunks;
-                    const int r = tap / p.kw, s = tap % p.kw;
-                    mbar_wait(&empty_bar[stage], phase ^ 1);
-                    uint8_t *sa = smem + stage * kStageBytes;
-                    uint8_t *sb = sa + kABytes;
-                    mbar_expect_tx(&full_bar[stage], kStageBytes);
-                    if (!p.stride2) {
-                        if (cc < p.split_chunks) tma_load_4d(sa, &tmA, &full_bar[stage], cc * KC, x0 + s - p.pad_w, y0 + r - p.pad_h, n0);
-                        else tma_load_4d(sa, &tmA2, &full_bar[stage], (cc - p.split_chunks) * KC, x0 + s - p.pad_w, y0 + r - p.pad_h, n0);
-                    } else {
-                        // input row 2*oy + r - pad = 2*h2 + py ; input col 2*ox + s - pad = 2*w2 + px
-                        const int dr = r - p.pad_h, ds = s - p.pad_w;
-                        const int py = (p.stride2 & 2) ? (dr & 1) : 0, px = (p.stride2 & 1) ? (ds & 1) : 0;
-                        const int hoff = (p.stride2 & 2) ? (dr - py) / 2 : dr, woff = (p.stride2 & 1) ? (ds - px) / 2 : ds;
-                        tma_load_5d(sa, &tmA, &full_bar[stage], px * p.in_ps + cc * KC, x0 + woff, py, y0 + hoff, n0);
-                    }
-                    if (p.mc) tma_load_3d_mc(sb + rank * (BN / 2 * KC * 2), &tmB, &full_bar[stage], cc * KC, nt * BN + (int)rank * (BN / 2), tap, (uint16_t)3);
-                    else tma_load_3d(sb, &tmB, &full_bar[stage], cc * KC, nt * BN, tap);
-                    if (++stage == kStages) { stage = 0; phase ^= 1; }
-                    if (dbg && tile == t_begin && kc == ks * k_per) dbg[1] = clock64() - t_start;     // first loads issued
+        // ===================== TMA producer (whole warp convergent, one elected lane issues; no divisions in the k loop) =====================
+        const uint32_t leader = elect_one();
+        const uint32_t s0 = smem_u32(smem);
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int tile = t_begin; tile < t_end; ++tile) {
+            const int ot = tile / ksplit, ks = tile - ot * ksplit;      // (output tile, K slice), slice fastest
+            const int nt = ot / mseq, mt = (ot - nt * mseq) * mstep + (int)rank;
+            const int xt = mt % p.tiles_w, yt = (mt / p.tiles_w) % p.tiles_h, nn = mt / (p.tiles_w * p.tiles_h);
+            const int x0 = xt * p.tw, y0 = yt * p.th, n0 = nn * p.tn;
+            const int kc0 = ks * k_per;
+            int tap = kc0 / p.cin_chunks, cc = kc0 - tap * p.cin_chunks;
+            int r = tap / p.kw, s = tap - r * p.kw;
+            for (int kc = 0; kc < k_per; ++kc) {
+                mbar_wait(&empty_bar[stage], phase ^ 1);
+                const uint32_t sa = s0 + (uint32_t)(stage * kStageBytes);
+                const uint32_t sb = sa + kABytes;
+                mbar_expect_tx_pred(leader, &full_bar[stage], kStageBytes);
+                if (!p.stride2) {
+                    const bool second = cc >= p.split_chunks;                       // K-chunks of the second input tensor (decoder: the skip)
+                    tma_load_4d_pred(leader, sa, second ? &tmA2 : &tmA, &full_bar[stage], (second ? cc - p.split_chunks : cc) * KC, x0 + s - p.pad_w,
+                                     y0 + r - p.pad_h, n0);
+                } else {
+                    // input row sh*oy + r - pad = sh*h2 + py ; input col sw*ox + s - pad = sw*w2 + px
+                    const int dr = r - p.pad_h, ds = s - p.pad_w;
+                    const int py = (p.stride2 & 2) ? (dr & 1) : 0, px = (p.stride2 & 1) ? (ds & 1) : 0;
+                    const int hoff = (p.stride2 & 2) ? (dr - py) / 2 : dr, woff = (p.stride2 & 1) ? (ds - px) / 2 : ds;
+                    tma_load_5d_pred(leader, sa, &tmA, &full_bar[stage], px * p.in_ps + cc * KC, x0 + woff, py, y0 + hoff, n0);
                 }
+                if (p.mc) {
+                    if (leader) tma_load_3d_mc(smem + stage * kStageBytes + kABytes + rank * (BN / 2 * KC * 2), &tmB, &full_bar[stage], cc * KC, nt * BN + (int)rank * (BN / 2), tap, (uint16_t)3);
+                } else tma_load_3d_pred(leader, sb, &tmB, &full_bar[stage], cc * KC, nt * BN, tap);
+                if (++stage == kStages) { stage = 0; phase ^= 1; }
+                if (dbg && lane == 0 && tile == t_begin && kc == 0) dbg[1] = clock64() - t_start;     // first loads issued
+                if (++cc == p.cin_chunks) { cc = 0; ++tap; if (++s == p.kw) { s = 0; ++r; } }
             }
-            if (dbg) dbg[2] = clock64() - t_start;                                                    // all loads issued
         }
+        if (dbg && lane == 0) dbg[2] = clock64() - t_start;                                            // all loads issued
     } else if (warp == 1) {
         // ===================== MMA issuer (whole warp convergent, one elected lane issues) =====================
         const uint32_t leader = elect_one();

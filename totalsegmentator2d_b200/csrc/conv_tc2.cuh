@@ -71,39 +71,40 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int u_end = (int)((long long)total_units * (blockIdx.x + 1) / gridDim.x);
 
     if (warp == 0) {
-        // ===================== TMA producer =====================
-        if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int u = u_begin; u < u_end; ++u) {
-                const int nt = u / mpairs, pi = u - nt * mpairs;
-                int x0[2], y0[2], n0[2];
+        // ===================== TMA producer (whole warp convergent, one elected lane issues; no divisions in the k loop) =====================
+        const uint32_t leader = elect_one();
+        const uint32_t s0 = smem_u32(smem);
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int u = u_begin; u < u_end; ++u) {
+            const int nt = u / mpairs, pi = u - nt * mpairs;
+            int x0[2], y0[2], n0[2];
 #pragma unroll
-                for (int t = 0; t < 2; ++t) {
-                    const int mt = 2 * pi + t;
-                    x0[t] = (mt % p.tiles_w) * p.tw; y0[t] = ((mt / p.tiles_w) % p.tiles_h) * p.th; n0[t] = mt / (p.tiles_w * p.tiles_h);
-                }
-                for (int kc = 0; kc < k_chunks; ++kc) {
-                    const int tap = kc / p.cin_chunks, cc = kc - tap * p.cin_chunks;
-                    const int r = tap / p.kw, s = tap - r * p.kw;
+            for (int t = 0; t < 2; ++t) {
+                const int mt = 2 * pi + t;
+                x0[t] = (mt % p.tiles_w) * p.tw; y0[t] = ((mt / p.tiles_w) % p.tiles_h) * p.th; n0[t] = mt / (p.tiles_w * p.tiles_h);
+            }
+            int r = 0, s = 0;
+            for (int tap = 0; tap < p.taps; ++tap) {
+                const int dr = r - p.pad_h, ds = s - p.pad_w;
+                const int py = (p.stride2 & 2) ? (dr & 1) : 0, px = (p.stride2 & 1) ? (ds & 1) : 0;
+                const int hoff = (p.stride2 & 2) ? (dr - py) / 2 : dr, woff = (p.stride2 & 1) ? (ds - px) / 2 : ds;
+                for (int cc = 0; cc < p.cin_chunks; ++cc) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
-                    uint8_t *sa = smem + stage * kStageBytes;
-                    mbar_expect_tx(&full_bar[stage], kStageBytes);
+                    const uint32_t sa = s0 + (uint32_t)(stage * kStageBytes);
+                    mbar_expect_tx_pred(leader, &full_bar[stage], kStageBytes);
+                    const bool second = cc >= p.split_chunks;                       // K-chunks of the second input tensor (decoder: the skip)
+                    const CUtensorMap *tm = second ? &tmA2 : &tmA;
+                    const int c0 = (second ? cc - p.split_chunks : cc) * KC;
 #pragma unroll
                     for (int t = 0; t < 2; ++t) {
-                        if (!p.stride2) {
-                            if (cc < p.split_chunks) tma_load_4d(sa + t * kABytes, &tmA, &full_bar[stage], cc * KC, x0[t] + s - p.pad_w, y0[t] + r - p.pad_h, n0[t]);
-                            else tma_load_4d(sa + t * kABytes, &tmA2, &full_bar[stage], (cc - p.split_chunks) * KC, x0[t] + s - p.pad_w, y0[t] + r - p.pad_h, n0[t]);
-                        } else {
-                            const int dr = r - p.pad_h, ds = s - p.pad_w;
-                            const int py = (p.stride2 & 2) ? (dr & 1) : 0, px = (p.stride2 & 1) ? (ds & 1) : 0;
-                            const int hoff = (p.stride2 & 2) ? (dr - py) / 2 : dr, woff = (p.stride2 & 1) ? (ds - px) / 2 : ds;
-                            tma_load_5d(sa + t * kABytes, &tmA, &full_bar[stage], px * p.in_ps + cc * KC, x0[t] + woff, py, y0[t] + hoff, n0[t]);
-                        }
+                        if (!p.stride2) tma_load_4d_pred(leader, sa + t * kABytes, tm, &full_bar[stage], c0, x0[t] + woff, y0[t] + hoff, n0[t]);
+                        else tma_load_5d_pred(leader, sa + t * kABytes, &tmA, &full_bar[stage], px * p.in_ps + cc * KC, x0[t] + woff, py, y0[t] + hoff, n0[t]);
                     }
-                    tma_load_3d(sa + 2 * kABytes, &tmB, &full_bar[stage], cc * KC, nt * BN, tap);
+                    tma_load_3d_pred(leader, sa + 2 * kABytes, &tmB, &full_bar[stage], cc * KC, nt * BN, tap);
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
+                if (++s == p.kw) { s = 0; ++r; }
             }
         }
     } else if (warp == 1) {
