@@ -508,6 +508,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
         };
         int cur_n = -1, cur_nt = -1;
+        int map_nt = -1, map_c0[kMyChunks];
+        long long map_off[kMyChunks];
         // tile walker (no divisions in the loop): this group's tiles are t_begin + e, e += estep
         const int estep = kAlt ? 2 : 1;
         int tile = t_begin + (kAlt ? grp : 0);
@@ -577,11 +579,23 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     tcgen05_fence_before();
                     mbar_arrive(&tmem_empty[buf]);
                 }
-                // column block -> (tap, channel) : transposed conv scatters tap (dy, dx) to pixel (y*my + dy, x*mx + dx)
+                // column block -> (tap, channel) : transposed conv scatters tap (dy, dx) to pixel (y*my + dy, x*mx + dx).  The mapping depends
+                // on the channel block only: its two integer divisions are redone when nt changes, not per tile (the epilogue of the
+                // 1-chunk-per-tile transposed convs is issue bound)
+                if (nt != map_nt) {
+#pragma unroll
+                    for (int cm = 0; cm < kMyChunks; ++cm) {
+                        const int gcol_m = nt * BN + (chunk0 + cm) * 32;
+                        const int tap_m = gcol_m / p.tap_cout, c0_m = gcol_m - tap_m * p.tap_cout;
+                        const int dy_m = tap_m / p.mx, dx_m = tap_m - dy_m * p.mx;
+                        map_c0[cm] = c0_m;
+                        map_off[cm] = ((long long)dy_m * p.Wfull + dx_m) * p.out_ps + c0_m;
+                    }
+                    map_nt = nt;
+                }
                 const int gcol = nt * BN + chunk * 32;
-                const int tap = gcol / p.tap_cout, c0 = gcol - tap * p.tap_cout;
-                const int dy = tap / p.mx, dx = tap - dy * p.mx;
-                DT *dst = opix + ((long long)dy * p.Wfull + dx) * p.out_ps + c0;
+                const int c0 = map_c0[c];
+                DT *dst = opix + map_off[c];
                 uint32_t pk[16];
                 uint64_t v[16];                  // fp32 values of this chunk (warp-reduced path only)
                 const bool tstat = do_stats && kThreadAcc && fast_stats;
