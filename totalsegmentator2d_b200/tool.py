@@ -330,7 +330,15 @@ class TS2D:
     def _streams(self):
         if getattr(self, "_h2d_stream", None) is None:
             self._h2d_stream = torch.cuda.Stream()
-            self._d2h_stream = torch.cuda.Stream()
+            # ``b200.copy_streams`` / $TS2D_COPY_STREAMS: 2 = uploads and downloads on separate streams (full duplex), 1 = one copy
+            # stream (a mask download never overlaps a volume upload), auto (default) = 1 when >= 4 ranks share the host.  Measured on
+            # the 8-GPU box (profiles/r02_h2d_ceiling_n8.json): with all ranks uploading, the slow ranks move 23.3 GB/s host -> device
+            # alone but 18.6 GB/s while 60 MB masks go the other way at the same time - 584 MB per study in 25.1 ms serialised against
+            # 28.2 ms overlapped; alone on the host a GPU has PCIe bandwidth to spare and full duplex costs nothing.
+            want = str(os.environ.get("TS2D_COPY_STREAMS", self._param.get("b200.copy_streams", "auto"))).lower()
+            if want == "auto":
+                want = "1" if int(os.environ.get("WORLD_SIZE", "1")) >= 4 else "2"
+            self._d2h_stream = self._h2d_stream if want == "1" else torch.cuda.Stream()
         return self._h2d_stream, self._d2h_stream
 
     @staticmethod
