@@ -433,7 +433,7 @@ def run_b200(args):
             nbytes_out = 0
             for res in ts.predict_batch(imgs[i % S] for i in range(n_steps * S)):
                 seg = res.get_segmentation()
-                nbytes_out = seg.array.nbytes
+                nbytes_out = int(res.data.get("d2h_bytes", seg.array.nbytes))     # bit-packed download (b200.pack_mask): the bytes that crossed PCIe
             return nbytes_out * S
 
         run_e2e(3)

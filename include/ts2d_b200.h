@@ -169,6 +169,12 @@ int ts2d_permute_channels(const uint8_t *src_dev, uint8_t *dst_dev, int64_t n_pi
  * perm_dev: int32[C], receives the permutation (the host reads it to name the channels). */
 int ts2d_merge_present_order(const uint8_t *src_dev, uint8_t *dst_dev, int64_t n_pix, int C, const uint8_t *present_dev,
                              const int *offsets_host, int n_models, int *perm_dev, ts2d_stream stream);
+/* Bit-packed transport of a 0/1 label mask (59.9 MB as uint8, 7.5 MB bit-packed; the reference has no
+ * counterpart - its masks go through gzip-compressed temp files, ts2d/core/inference/prediction_worker.py:235-240).
+ * pack: dst_dev[i] bit k = (src_dev[8i + k] != 0), ceil(n_bytes / 8) output bytes; src 16-byte aligned.
+ * unpack (HOST memory, no CUDA call): out[j] = bit (j & 7) of packed[j / 8], with up to `threads` worker threads. */
+int ts2d_pack_mask_bits(const uint8_t *src_dev, uint8_t *dst_dev, int64_t n_bytes, ts2d_stream stream);
+int ts2d_unpack_mask_bits_host(const uint8_t *packed_host, uint8_t *out_host, int64_t n_bytes, int threads);
 /* re-allocates the workspace for a larger/smaller max_batch (weights are kept) */
 int ts2d_unet_resize(ts2d_unet *u, int max_batch);
 /* number of kernel launches this engine issued since creation (bench.py's gpu_launches) */

@@ -212,3 +212,30 @@ def test_full_size_study_flip_equivariance_and_determinism():
         else:
             assert torch.equal(pa, torch.flip(rb["projections"], dims=[-2]))
         torch.cuda.synchronize()
+
+
+def test_packed_mask_download_is_lossless(zoo, monkeypatch):
+    """ts2d_pack_mask_bits (device) + ts2d_unpack_mask_bits_host: bit k of packed byte i = mask byte 8i + k, for lengths that are and are not
+    multiples of 16; and TS2D.predict with b200.pack_mask returns the same merged segmentation bytes as the plain uint8 download."""
+    from totalsegmentator2d_b200 import ops
+    from totalsegmentator2d_b200.image import Image
+    from totalsegmentator2d_b200.tool import TS2D
+    g = torch.Generator().manual_seed(1)
+    for shape in [(37, 53, 117), (8, 16), (5,), (1000, 64, 9)]:
+        m = (torch.rand(shape, generator=g) > 0.6).to(torch.uint8).cuda()
+        packed = ops.pack_mask_bits(m).cpu().numpy()
+        want = np.packbits(m.cpu().numpy().reshape(-1), bitorder="little")
+        assert np.array_equal(packed, want), shape
+        assert np.array_equal(ops.unpack_mask_bits_host(packed, shape), m.cpu().numpy())
+    root, groups = zoo
+    rng = np.random.default_rng(3)
+    vol = np.clip(np.round(rng.normal(-200, 500, size=(90, 30, 70))), -1024, 3071).astype(np.int16)
+    img = Image(vol, (1.5, 1.5, 1.5), (0, 0, 0), np.eye(3).reshape(-1))
+    segs = []
+    for pack in ("0", "1"):
+        monkeypatch.setenv("TS2D_PACK_MASK", pack)
+        with TS2D(key="ts2d", models_root=root) as ts:
+            res = ts.predict(img)
+            seg = res.get_segmentation()
+            segs.append((np.array(seg.array), dict((k, seg.GetMetaData(k)) for k in seg.GetMetaDataKeys())))
+    assert np.array_equal(segs[0][0], segs[1][0]) and segs[0][1] == segs[1][1]

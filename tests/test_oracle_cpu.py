@@ -297,3 +297,16 @@ def test_visual_restatement_properties():
     a = np.array([[0.0, 50.0], [100.0, 25.0]], np.float32)
     assert ovis.visual_intensity(a, a.shape, (1, 1), resample=False).tolist() == [[0, 127], [255, 63]]
     assert np.array_equal(ovis.visual_intensity(a, a.shape, (1.0, 1.0)), ovis.visual_intensity(a, a.shape, (1, 1), resample=False))
+
+
+def test_unpack_mask_bits_host_is_numpy_unpackbits():
+    """host half of the bit-packed mask transport (no GPU call): ts2d_unpack_mask_bits_host == np.unpackbits(bitorder='little'), for
+    lengths that are not multiples of 8 and for a study-sized mask with several threads"""
+    from totalsegmentator2d_b200 import ops
+    rng = np.random.default_rng(12)
+    for n, threads in ((0, 1), (5, 1), (8, 2), (117 * 13, 4), (1000 * 512 * 3, 4), (1 << 21, 8)):
+        m = (rng.random(n) > 0.7).astype(np.uint8)
+        packed = np.packbits(m, bitorder="little")
+        assert np.array_equal(ops.unpack_mask_bits_host(packed, (n,), threads=threads), m), n
+    with pytest.raises(Exception):
+        ops.unpack_mask_bits_host(np.zeros(3, np.uint8), (100,))

@@ -81,6 +81,8 @@ _PROTOS = {
     "ts2d_visual_intensity": (_i, [_vp, _i, _i, _i, _i, C.c_double, C.c_double, _i, C.c_double, C.c_double, _i, _i, _vp, _vp, _vp, _vp]),
     "ts2d_merge_present_order": (_i, [_vp, _vp, _i64, _i, _vp, _ip, _i, _vp, _vp]),
     "ts2d_unet_launch_count": (_i64, [_vp]),
+    "ts2d_pack_mask_bits": (_i, [_vp, _vp, _i64, _vp]),
+    "ts2d_unpack_mask_bits_host": (_i, [_vp, _vp, _i64, _i]),
     "ts2d_unet_direct_layer_count": (_i, [_vp]),
     "ts2d_unet_check_guards": (_i, [_vp]),
     "ts2d_unet_guard_count": (_i, [_vp]),

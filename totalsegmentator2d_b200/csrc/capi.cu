@@ -1,6 +1,9 @@
 // C-ABI plumbing shared by every entry point: thread-local error slot, launch counter, device check.
 #include <stdarg.h>
 
+#include <thread>
+#include <vector>
+
 #include "common.cuh"
 
 namespace ts2d {
@@ -42,5 +45,76 @@ extern "C" int ts2d_device_check(int device) {
         ts2d::set_error("sm_100a kernel image does not load on device %d: %s", device, cudaGetErrorString(e));
         return TS2D_ERR_DEVICE;
     }
+    return TS2D_OK;
+}
+
+// ---- bit-packed label masks ("59.9 MB as uint8; 7.5 MB bit-packed") ---------------------------------------------
+// The merged mask holds one 0/1 byte per (pixel, label).  On a host whose PCIe / memory path is shared by several GPUs the 60 MB
+// download competes with the next study's 524 MB upload: ts2d_pack_mask_bits folds 8 bytes into one on the
+// device (byte i of the output holds mask bytes 8i .. 8i+7, least significant bit first), the host copy is 8x smaller, and
+// ts2d_unpack_mask_bits_host restores the uint8 array the API returns.
+namespace ts2d {
+__global__ void __launch_bounds__(256) pack_bits_kernel(const uint8_t *__restrict__ src, uint8_t *__restrict__ dst, long long n_out, long long n_in) {
+    // one thread: 16 input bytes -> 2 output bytes (16-byte loads; the tail is handled byte-wise)
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;      // index of a 16-byte input group
+    const long long in0 = i * 16;
+    if (in0 >= n_in) return;
+    if (in0 + 16 <= n_in) {
+        const uint4 v = *reinterpret_cast<const uint4 *>(src + in0);
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+        uint32_t bits = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            // bytes are 0 / 1 (any non-zero counts): gather bit 0 of the four bytes
+            uint32_t x = w[k];
+            x |= x >> 4; x |= x >> 2; x |= x >> 1;        // bit 0 of every byte = OR of its bits
+            x &= 0x01010101u;
+            bits |= (((x * 0x01020408u) >> 24) & 0xFu) << (4 * k);      // bytes b0..b3 -> bits 0..3 (no carries: every product bit is distinct)
+        }
+        dst[2 * i] = (uint8_t)(bits & 0xFF);
+        dst[2 * i + 1] = (uint8_t)(bits >> 8);
+    } else {
+        for (long long o = 2 * i; o < n_out && o < 2 * i + 2; ++o) {
+            uint32_t b = 0;
+            for (int k = 0; k < 8; ++k) {
+                const long long j = o * 8 + k;
+                if (j < n_in && src[j]) b |= 1u << k;
+            }
+            dst[o] = (uint8_t)b;
+        }
+    }
+}
+}  // namespace ts2d
+
+extern "C" int ts2d_pack_mask_bits(const uint8_t *src_dev, uint8_t *dst_dev, int64_t n_bytes, ts2d_stream stream) {
+    TS2D_REQUIRE(src_dev && dst_dev && n_bytes >= 0, "ts2d_pack_mask_bits: bad arguments");
+    TS2D_REQUIRE(((uintptr_t)src_dev) % 16 == 0, "ts2d_pack_mask_bits: the mask must be 16-byte aligned");
+    if (n_bytes == 0) return TS2D_OK;
+    const long long groups = (n_bytes + 15) / 16, n_out = (n_bytes + 7) / 8;
+    ts2d::pack_bits_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, (cudaStream_t)stream>>>(src_dev, dst_dev, n_out, n_bytes);
+    TS2D_LAUNCH_CHECK();
+    return TS2D_OK;
+}
+
+extern "C" int ts2d_unpack_mask_bits_host(const uint8_t *packed, uint8_t *out, int64_t n_bytes, int threads) {
+    TS2D_REQUIRE(packed && out && n_bytes >= 0, "ts2d_unpack_mask_bits_host: bad arguments");
+    const int64_t n_full = n_bytes / 8;                 // whole input bytes -> 8 output bytes each
+    auto work = [&](int64_t lo, int64_t hi) {
+        for (int64_t i = lo; i < hi; ++i) {
+            // byte k of x = bit k of packed[i]: replicate, isolate one bit per byte, turn "non-zero" into 1 (no carries between bytes)
+            uint64_t x = (uint64_t)packed[i] * 0x0101010101010101ULL;
+            x &= 0x8040201008040201ULL;
+            x = ((x + 0x7F7F7F7F7F7F7F7FULL) >> 7) & 0x0101010101010101ULL;
+            memcpy(out + 8 * i, &x, 8);                 // little-endian hosts (x86-64 / aarch64)
+        }
+    };
+    const int nt = (int)std::max<int64_t>(1, std::min<int64_t>(threads, n_full / (1 << 16)));
+    if (nt <= 1) work(0, n_full);
+    else {
+        std::vector<std::thread> pool;
+        for (int t = 0; t < nt; ++t) pool.emplace_back(work, n_full * t / nt, n_full * (t + 1) / nt);
+        for (auto &th : pool) th.join();
+    }
+    for (int64_t j = n_full * 8; j < n_bytes; ++j) out[j] = (packed[j / 8] >> (j & 7)) & 1;
     return TS2D_OK;
 }

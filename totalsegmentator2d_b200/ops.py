@@ -146,6 +146,28 @@ def merge_present_order(src: torch.Tensor, present: torch.Tensor, offsets: Seque
     return out, perm
 
 
+def pack_mask_bits(mask: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """0/1 uint8 mask (any shape, contiguous) -> ceil(numel / 8) bytes on the device, bit k of byte i = mask byte 8i + k"""
+    lib = L.load()
+    n = mask.numel()
+    if out is None:
+        out = torch.empty((n + 7) // 8, dtype=torch.uint8, device=mask.device)
+    L.check(lib.ts2d_pack_mask_bits(_dev(mask, "mask"), _dev(out, "out"), n, L.stream_ptr()), "ts2d_pack_mask_bits")
+    return out
+
+
+def unpack_mask_bits_host(packed: np.ndarray, shape, threads: int = 4) -> np.ndarray:
+    """host side of pack_mask_bits: packed uint8 array -> uint8 array of ``shape`` holding 0 / 1 (no GPU involved)"""
+    lib = L.load(check_device=False)
+    n = int(np.prod(shape))
+    packed = np.ascontiguousarray(packed, dtype=np.uint8)
+    if packed.size < (n + 7) // 8:
+        raise L.TS2DError("unpack_mask_bits_host: {} packed bytes cannot hold {} mask bytes".format(packed.size, n))
+    out = np.empty(n, dtype=np.uint8)
+    L.check(lib.ts2d_unpack_mask_bits_host(packed.ctypes.data, out.ctypes.data, n, int(threads)), "ts2d_unpack_mask_bits_host")
+    return out.reshape(shape)
+
+
 def visual_labels(mask: torch.Tensor, new_hw, ratio_yx, palette: np.ndarray) -> torch.Tensor:
     """create_visual for a multi-component mask (reference ts2d/core/util/image.py:431-440): [H][W][C] uint8 -> RGB uint8 [H2][W2][3]."""
     lib = L.load()
