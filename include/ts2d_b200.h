@@ -175,6 +175,11 @@ int ts2d_merge_present_order(const uint8_t *src_dev, uint8_t *dst_dev, int64_t n
  * unpack (HOST memory, no CUDA call): out[j] = bit (j & 7) of packed[j / 8], with up to `threads` worker threads. */
 int ts2d_pack_mask_bits(const uint8_t *src_dev, uint8_t *dst_dev, int64_t n_bytes, ts2d_stream stream);
 int ts2d_unpack_mask_bits_host(const uint8_t *packed_host, uint8_t *out_host, int64_t n_bytes, int threads);
+/* Upload buffers for the volume ingest (the reference decodes into pageable memory with sitk.ReadImage,
+ * ts2d/core/util/image.py:225-238): page-locked host memory, optionally write-combined (written once by the CPU, read once by the
+ * GPU over PCIe without cache snoops). Returns NULL on failure (ts2d_last_error). */
+void *ts2d_host_alloc(size_t bytes, int write_combined);
+int ts2d_host_free(void *ptr);
 /* re-allocates the workspace for a larger/smaller max_batch (weights are kept) */
 int ts2d_unet_resize(ts2d_unet *u, int max_batch);
 /* number of kernel launches this engine issued since creation (bench.py's gpu_launches) */

@@ -31,9 +31,18 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     nbytes = 1000 * 512 * 512 * 2
     mbytes = 1000 * 512 * 117
-    host = [torch.empty(nbytes, dtype=torch.uint8).pin_memory() for _ in range(2)]
-    for h in host:
-        h.fill_(3)
+    wc = os.environ.get("H2D_WC", "0") == "1"          # write-combined upload buffers (ops.UploadBuffer) instead of torch's pinned memory
+    if wc:
+        from totalsegmentator2d_b200 import ops
+        import numpy as np
+        keep = [ops.UploadBuffer((nbytes,), np.uint8, write_combined=True) for _ in range(2)]
+        for k in keep:
+            k.array[:] = 3
+        host = [torch.from_numpy(k.array) for k in keep]
+    else:
+        host = [torch.empty(nbytes, dtype=torch.uint8).pin_memory() for _ in range(2)]
+        for h in host:
+            h.fill_(3)
     dev = [torch.empty(nbytes, dtype=torch.uint8, device="cuda") for _ in range(2)]
     mdev = torch.zeros(mbytes, dtype=torch.uint8, device="cuda")
     mhost = torch.empty(mbytes, dtype=torch.uint8).pin_memory()
@@ -81,7 +90,7 @@ def main():
         # ranks run concurrently for (about) the same wall time: aggregate = sum of the per-rank rates
         out[mode] = {"per_rank_gbs": [round(v, 2) for v in per], "aggregate_gbs": round(sum(per), 2), "min_rank_gbs": round(min(per), 2)}
     if rank == 0:
-        print(json.dumps({"probe": "h2d_ceiling", "ranks": world, "bytes_per_copy": nbytes, "reps": reps, **out}))
+        print(json.dumps({"probe": "h2d_ceiling", "write_combined": wc, "ranks": world, "bytes_per_copy": nbytes, "reps": reps, **out}))
     if world > 1:
         import torch.distributed as dist
         dist.destroy_process_group()

@@ -118,3 +118,19 @@ extern "C" int ts2d_unpack_mask_bits_host(const uint8_t *packed, uint8_t *out, i
     for (int64_t j = n_full * 8; j < n_bytes; ++j) out[j] = (packed[j / 8] >> (j & 7)) & 1;
     return TS2D_OK;
 }
+
+// ---- upload buffers (input ingest) ---------------------------------------------------------------------------------
+// Page-locked host memory for volumes that are written once by the CPU (decoded from disk) and read once by the GPU.  write_combined = 1
+// asks for cudaHostAllocWriteCombined: the memory is not snooped during the PCIe transfer (CPU reads of it are slow - it is an upload
+// buffer, not a working array).
+extern "C" void *ts2d_host_alloc(size_t bytes, int write_combined) {
+    void *p = nullptr;
+    cudaError_t e = cudaHostAlloc(&p, bytes, write_combined ? cudaHostAllocWriteCombined : cudaHostAllocDefault);
+    if (e != cudaSuccess) { ts2d::set_error("cudaHostAlloc(%zu bytes) failed: %s", bytes, cudaGetErrorString(e)); return nullptr; }
+    return p;
+}
+extern "C" int ts2d_host_free(void *p) {
+    if (!p) return TS2D_OK;
+    TS2D_CHECK_CUDA(cudaFreeHost(p));
+    return TS2D_OK;
+}

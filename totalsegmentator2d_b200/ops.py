@@ -146,6 +146,34 @@ def merge_present_order(src: torch.Tensor, present: torch.Tensor, offsets: Seque
     return out, perm
 
 
+class UploadBuffer:
+    """Page-locked (optionally write-combined) host array for a volume that is decoded once and uploaded once:
+    ``buf = UploadBuffer((1000, 512, 512), np.int16); buf.array[...] = volume; Image(buf.array, ...)``.  torch recognises the memory as
+    pinned, so ``TS2D.predict`` uploads it with an asynchronous copy.  Keep the object alive while ``array`` is in use."""
+
+    def __init__(self, shape, dtype=np.int16, write_combined: bool = True):
+        import ctypes
+        lib = L.load(check_device=True)
+        self._lib = lib
+        self.nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        self._ptr = lib.ts2d_host_alloc(self.nbytes, int(bool(write_combined)))
+        if not self._ptr:
+            raise L.TS2DError("ts2d_host_alloc: " + L.last_error())
+        self.array = np.frombuffer((ctypes.c_uint8 * self.nbytes).from_address(self._ptr), dtype=dtype).reshape(shape)
+
+    def close(self):
+        if getattr(self, "_ptr", None):
+            self.array = None
+            self._lib.ts2d_host_free(self._ptr)
+            self._ptr = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 def pack_mask_bits(mask: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """0/1 uint8 mask (any shape, contiguous) -> ceil(numel / 8) bytes on the device, bit k of byte i = mask byte 8i + k"""
     lib = L.load()
