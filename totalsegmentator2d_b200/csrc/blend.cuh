@@ -62,133 +62,151 @@ __global__ void __launch_bounds__(kBlend2Threads, F <= 32 ? 4 : 2) blend_head_v2
     }
     __syncthreads();
 
-    // ---------------- phase 1: blend ----------------
+    // PERSISTENT blocks: the prologue above (head weights + InstanceNorm table into shared memory) was 9 % of the executed instructions
+    // and 15 % of the stall samples when every 64-pixel group had its own block (profiles/r02_blend_ncu.txt); now a block walks
+    // groups blockIdx.x, blockIdx.x + gridDim.x, ...
     const int pl = tid / LPP, q = tid % LPP;                    // local pixel, channel block (8 channels)
     const long long npix_full = (long long)full_h * full_w;
-    const long long gp = (long long)blockIdx.x * PPB + pl;      // pixel of the full output image (mask space) or of the crop (no mask)
-    const bool in_img = gp < npix_full;
-    const int fy = in_img ? (int)(gp / full_w) : 0, fx = in_img ? (int)(gp % full_w) : 0;
-    // crop coordinates (the network's grid): the mask window starts at (h0, w0)
-    const int y = fy - (p.mask ? p.h0 : 0), x = fx - (p.mask ? p.w0 : 0);
-    const bool active = in_img && y >= 0 && y < p.h && x >= 0 && x < p.w;
-    const int yp = y + p.pad_top, xp = x + p.pad_left;
-    float acc[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) acc[k] = 0.f;
-    float wsum = 0.f;
+    const long long n_groups = (npix_full + PPB - 1) / PPB;
     const T *feat = reinterpret_cast<const T *>(p.feat);
     const float inv_m = 1.0f / (float)M;
     const float slope = p.slope;
+    const uint64_t slope2 = f32x2_pack(slope, slope);
     const bool slope01 = slope >= 0.f && slope <= 1.f;          // LeakyReLU(y) == max(y, slope * y)
-    const long long img_stride = (long long)p.Ph * p.Pw * F;
-    if (active) {
-        for (int t = 0; t < p.T; ++t) {
-            const int ly = yp - tl.yx[t][0], lx = xp - tl.yx[t][1];
-            if (ly < 0 || ly >= p.Ph || lx < 0 || lx >= p.Pw) continue;
-            const float g = __ldg(p.gauss + ly * p.Pw + lx);
-            wsum += g;
-            const float gm = g * inv_m;
-            uint4 v[M];
-            const T *tbase = feat + (long long)(t * M) * img_stride + q * 8;
-            const int fy_ = p.Ph - 1 - ly, fx_ = p.Pw - 1 - lx;
+    const int img_stride = p.Ph * p.Pw * F;                     // elements of one tile image (fits 32 bits: 512 x 512 x 64 = 2^24)
+    const int hp = tid % PPB, hg = tid / PPB;                   // phase 2: pixel, head group (a warp shares hg: weight loads broadcast)
+    const int hpg = (heads + G - 1) / G;                        // heads per group
+    const int c_lo = hg * hpg, c_hi = min(heads, c_lo + hpg);
+
+    for (long long group = blockIdx.x; group < n_groups; group += gridDim.x) {
+        // ---------------- phase 1: blend ----------------
+        const long long gp = group * PPB + pl;                  // pixel of the full output image (mask space) or of the crop (no mask)
+        const bool in_img = gp < npix_full;
+        const int fy = in_img ? (int)(gp / full_w) : 0, fx = in_img ? (int)(gp - (long long)fy * full_w) : 0;
+        // crop coordinates (the network's grid): the mask window starts at (h0, w0)
+        const int y = fy - (p.mask ? p.h0 : 0), x = fx - (p.mask ? p.w0 : 0);
+        const bool active = in_img && y >= 0 && y < p.h && x >= 0 && x < p.w;
+        const int yp = y + p.pad_top, xp = x + p.pad_left;
+        uint64_t acc2[4];
 #pragma unroll
-            for (int m = 0; m < M; ++m) {
-                const bool fh = MM == 3 ? (m & 1) != 0 : (MM == 1 && m == 1);
-                const bool fw = MM == 3 ? (m & 2) != 0 : (MM == 2 && m == 1);
-                v[m] = __ldg(reinterpret_cast<const uint4 *>(tbase + m * img_stride + ((long long)(fh ? fy_ : ly) * p.Pw + (fw ? fx_ : lx)) * F));
-            }
+        for (int k = 0; k < 4; ++k) acc2[k] = 0ull;
+        float wsum = 0.f;
+        if (active) {
+            for (int t = 0; t < p.T; ++t) {
+                const int ly = yp - tl.yx[t][0], lx = xp - tl.yx[t][1];
+                if (ly < 0 || ly >= p.Ph || lx < 0 || lx >= p.Pw) continue;
+                const float g = __ldg(p.gauss + ly * p.Pw + lx);
+                wsum += g;
+                const float gm = g * inv_m;
+                const uint64_t gm2 = f32x2_pack(gm, gm);
+                uint4 v[M];
+                const T *tbase = feat + (long long)(t * M) * img_stride + q * 8;
+                // the four mirror variants of a tile read (row, col) in {ly, Ph-1-ly} x {lx, Pw-1-lx}: 32-bit offsets inside the tile's M images
+                const int r0 = ly * p.Pw, r1 = (p.Ph - 1 - ly) * p.Pw, c0 = lx, c1 = p.Pw - 1 - lx;
 #pragma unroll
-            for (int m = 0; m < M; ++m) {
-                {
+                for (int m = 0; m < M; ++m) {
+                    const bool fh = MM == 3 ? (m & 1) != 0 : (MM == 1 && m == 1);
+                    const bool fw = MM == 3 ? (m & 2) != 0 : (MM == 2 && m == 1);
+                    v[m] = __ldg(reinterpret_cast<const uint4 *>(tbase + (m * img_stride + ((fh ? r1 : r0) + (fw ? c1 : c0)) * F)));
+                }
+#pragma unroll
+                for (int m = 0; m < M; ++m) {
                     const uint32_t *w = reinterpret_cast<const uint32_t *>(&v[m]);
-                    float f[8];
+                    uint64_t f2[4];
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) { const float2 e = unpack2<T>(w[j]); f[2 * j] = e.x; f[2 * j + 1] = e.y; }
+                    for (int j = 0; j < 4; ++j) { const float2 e = unpack2<T>(w[j]); f2[j] = f32x2_pack(e.x, e.y); }
                     if (p.feat_ss) {
-                        float scv[8], shv[8];
+                        uint64_t sc2[4], sh2[4];
                         if (ss_smem) {
                             const float4 *sc = reinterpret_cast<const float4 *>(s_ss + (t * M + m) * 2 * F + q * 8);
                             const float4 *sh = reinterpret_cast<const float4 *>(s_ss + (t * M + m) * 2 * F + F + q * 8);
                             const float4 a0 = sc[0], a1 = sc[1], b0 = sh[0], b1 = sh[1];
-                            scv[0] = a0.x; scv[1] = a0.y; scv[2] = a0.z; scv[3] = a0.w; scv[4] = a1.x; scv[5] = a1.y; scv[6] = a1.z; scv[7] = a1.w;
-                            shv[0] = b0.x; shv[1] = b0.y; shv[2] = b0.z; shv[3] = b0.w; shv[4] = b1.x; shv[5] = b1.y; shv[6] = b1.z; shv[7] = b1.w;
+                            sc2[0] = f32x2_pack(a0.x, a0.y); sc2[1] = f32x2_pack(a0.z, a0.w); sc2[2] = f32x2_pack(a1.x, a1.y); sc2[3] = f32x2_pack(a1.z, a1.w);
+                            sh2[0] = f32x2_pack(b0.x, b0.y); sh2[1] = f32x2_pack(b0.z, b0.w); sh2[2] = f32x2_pack(b1.x, b1.y); sh2[3] = f32x2_pack(b1.z, b1.w);
                         } else {
                             // too many tiles for shared memory: the pair layout {sc, sc, sh, sh} straight from global memory (L1 hits)
                             const float4 *ss = reinterpret_cast<const float4 *>(p.feat_ss) + (long long)(t * M + m) * (F / 2) + q * 4;
 #pragma unroll
                             for (int j = 0; j < 4; ++j) {
                                 const float4 c4 = __ldg(ss + j);
-                                scv[2 * j] = c4.x; scv[2 * j + 1] = c4.y; shv[2 * j] = c4.z; shv[2 * j + 1] = c4.w;
+                                sc2[j] = f32x2_pack(c4.x, c4.y); sh2[j] = f32x2_pack(c4.z, c4.w);
                             }
                         }
 #pragma unroll
-                        for (int k = 0; k < 8; ++k) {
-                            const float yv = fmaf(f[k], scv[k], shv[k]);
-                            f[k] = slope01 ? fmaxf(yv, yv * slope) : (yv > 0.f ? yv : yv * slope);
+                        for (int j = 0; j < 4; ++j) {
+                            // same roundings as norm_act_kernel: fma, then LeakyReLU
+                            const uint64_t yv = f32x2_fma(f2[j], sc2[j], sh2[j]);
+                            if (slope01) {
+                                const uint64_t ys = f32x2_mul(yv, slope2);
+                                f2[j] = f32x2_pack(fmaxf(f32x2_lo(yv), f32x2_lo(ys)), fmaxf(f32x2_hi(yv), f32x2_hi(ys)));
+                            } else {
+                                const float a = f32x2_lo(yv), b = f32x2_hi(yv);
+                                f2[j] = f32x2_pack(a > 0.f ? a : a * slope, b > 0.f ? b : b * slope);
+                            }
                         }
                     }
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) acc[k] = fmaf(gm, f[k], acc[k]);
+                    for (int j = 0; j < 4; ++j) acc2[j] = f32x2_fma(gm2, f2[j], acc2[j]);
                 }
             }
         }
-    }
-    {
-        const float inv = active ? 1.0f / wsum : 0.f;
-        float4 *dst = reinterpret_cast<float4 *>(s_feat + pl * FS + q * 8);
-        dst[0] = make_float4(acc[0] * inv, acc[1] * inv, acc[2] * inv, acc[3] * inv);
-        dst[1] = make_float4(acc[4] * inv, acc[5] * inv, acc[6] * inv, acc[7] * inv);
-    }
-    if (q == 0) s_base[pl] = in_img ? (active ? 1LL : 0LL) | (((long long)fy * p.W0 + fx) * p.ch_total + p.ch_off) << 1 : -1LL;
-    __syncthreads();
+        {
+            const float inv = active ? 1.0f / wsum : 0.f;
+            float4 *dst = reinterpret_cast<float4 *>(s_feat + pl * FS + q * 8);
+            dst[0] = make_float4(f32x2_lo(acc2[0]) * inv, f32x2_hi(acc2[0]) * inv, f32x2_lo(acc2[1]) * inv, f32x2_hi(acc2[1]) * inv);
+            dst[1] = make_float4(f32x2_lo(acc2[2]) * inv, f32x2_hi(acc2[2]) * inv, f32x2_lo(acc2[3]) * inv, f32x2_hi(acc2[3]) * inv);
+        }
+        if (q == 0) s_base[pl] = in_img ? (active ? 1LL : 0LL) | (((long long)fy * p.W0 + fx) * p.ch_total + p.ch_off) << 1 : -1LL;
+        __syncthreads();
 
-    // ---------------- phase 2: head ----------------
-    const int hp = tid % PPB, hg = tid / PPB;                   // pixel, head group (a warp shares hg: weight loads broadcast)
-    const int hpg = (heads + G - 1) / G;                        // heads per group
-    const int c_lo = hg * hpg, c_hi = min(heads, c_lo + hpg);
-    const long long hbase = s_base[hp];
-    const bool h_in = hbase >= 0, h_act = h_in && (hbase & 1);
-    {
-        float fv[F];
-        const float4 *fr = reinterpret_cast<const float4 *>(s_feat + hp * FS);
+        // ---------------- phase 2: head ----------------
+        const long long hbase = s_base[hp];
+        const bool h_in = hbase >= 0, h_act = h_in && (hbase & 1);
+        {
+            // fp32x2 dot products: the feature row and the weight row are read as pairs (f[2k], f[2k+1]) x (w[2k], w[2k+1]) into two
+            // pair accumulators = 4 partial sums (k mod 4, the association of the fp32 reference head kernel)
+            uint64_t fv2[F / 2];
+            const float4 *fr = reinterpret_cast<const float4 *>(s_feat + hp * FS);
 #pragma unroll
-        for (int k = 0; k < F / 4; ++k) { const float4 t4 = fr[k]; fv[4 * k] = t4.x; fv[4 * k + 1] = t4.y; fv[4 * k + 2] = t4.z; fv[4 * k + 3] = t4.w; }
-        // crop-space coordinates of this thread's pixel (logits output)
-        const long long gp2 = (long long)blockIdx.x * PPB + hp;
-        const int fy2 = (int)(gp2 / full_w), fx2 = (int)(gp2 % full_w);
-        const int y2 = fy2 - (p.mask ? p.h0 : 0), x2 = fx2 - (p.mask ? p.w0 : 0);
-        for (int c = c_lo; c < c_hi; ++c) {
-            const float4 *hw = reinterpret_cast<const float4 *>(s_w + c * F);
-            float d0 = 0.f, d1 = 0.f, d2 = 0.f, d3 = 0.f;
+            for (int k = 0; k < F / 4; ++k) { const float4 t4 = fr[k]; fv2[2 * k] = f32x2_pack(t4.x, t4.y); fv2[2 * k + 1] = f32x2_pack(t4.z, t4.w); }
+            // crop-space coordinates of this thread's pixel (logits output)
+            const long long gp2 = group * PPB + hp;
+            const int fy2 = (int)(gp2 / full_w), fx2 = (int)(gp2 - (long long)fy2 * full_w);
+            const int y2 = fy2 - (p.mask ? p.h0 : 0), x2 = fx2 - (p.mask ? p.w0 : 0);
+            for (int c = c_lo; c < c_hi; ++c) {
+                const float4 *hw = reinterpret_cast<const float4 *>(s_w + c * F);
+                uint64_t d01 = 0ull, d23 = 0ull;
 #pragma unroll
-            for (int k = 0; k < F / 4; ++k) {
-                const float4 wq = hw[k];
-                d0 = fmaf(wq.x, fv[4 * k], d0); d1 = fmaf(wq.y, fv[4 * k + 1], d1);
-                d2 = fmaf(wq.z, fv[4 * k + 2], d2); d3 = fmaf(wq.w, fv[4 * k + 3], d3);
-            }
-            const float v = s_b[c] + ((d0 + d1) + (d2 + d3));
-            const bool on = h_act && v > 0.f;
-            if (p.logits && h_act) p.logits[((long long)c * p.h + y2) * p.w + x2] = v;
-            if (p.mask) s_mask[hp * heads + c] = on ? 1 : 0;
-            if (p.present) {
-                const unsigned any = __ballot_sync(0xffffffffu, on);
-                if (any && (tid & 31) == 0) s_any[c] = 1;
+                for (int k = 0; k < F / 4; ++k) {
+                    const float4 wq = hw[k];
+                    d01 = f32x2_fma(f32x2_pack(wq.x, wq.y), fv2[2 * k], d01);
+                    d23 = f32x2_fma(f32x2_pack(wq.z, wq.w), fv2[2 * k + 1], d23);
+                }
+                const float v = s_b[c] + ((f32x2_lo(d01) + f32x2_hi(d01)) + (f32x2_lo(d23) + f32x2_hi(d23)));
+                const bool on = h_act && v > 0.f;
+                if (p.logits && h_act) p.logits[((long long)c * p.h + y2) * p.w + x2] = v;
+                if (p.mask) s_mask[hp * heads + c] = on ? 1 : 0;
+                if (p.present) {
+                    const unsigned any = __ballot_sync(0xffffffffu, on);
+                    if (any && (tid & 31) == 0) s_any[c] = 1;
+                }
             }
         }
+        __syncthreads();
+        // ---------------- phase 3: mask bytes ----------------
+        if (p.mask) {
+            const int total = PPB * heads;
+            for (int i = tid; i < total; i += kBlend2Threads) {
+                const int pp = i / heads, c = i - pp * heads;
+                const long long b = s_base[pp];
+                if (b >= 0) p.mask[(b >> 1) + c] = s_mask[i];
+            }
+        }
+        __syncthreads();                                        // s_feat / s_base / s_mask are rewritten by the next group
     }
-    __syncthreads();
     if (p.present)
         for (int c = tid; c < heads; c += kBlend2Threads)
             if (s_any[c] && __ldcg(p.present + p.ch_off + c) == 0) p.present[p.ch_off + c] = 1;
-    // ---------------- phase 3: mask bytes ----------------
-    if (p.mask) {
-        const int total = PPB * heads;
-        for (int i = tid; i < total; i += kBlend2Threads) {
-            const int pp = i / heads, c = i - pp * heads;
-            const long long b = s_base[pp];
-            if (b >= 0) p.mask[(b >> 1) + c] = s_mask[i];
-        }
-    }
 }
 
 template <int F> constexpr size_t blend2_smem_bytes(int heads, int n_img, bool ss) {

@@ -1260,7 +1260,8 @@ static int launch_blend2_inst(const BlendParams &p, const int *tile_yx_host, int
     const long long npix = (long long)full_h * full_w;
     TileListT<CAP> tl;
     fill_tile_list(tl, tile_yx_host, p.T);
-    const unsigned grid = (unsigned)ceil_div(npix, PPB);
+    // persistent blocks: four 256-thread blocks per SM walk the pixel groups (F <= 32; two per SM at F = 64: launch bounds of the kernel)
+    const unsigned grid = (unsigned)std::min<long long>(ceil_div(npix, PPB), (long long)kNumSMs * (F <= 32 ? 4 : 2));
     switch (p.mirror_mask) {
         case 0: blend_head_v2_kernel<T, F, CAP, 0><<<grid, kBlend2Threads, smem, st>>>(p, tl, full_h, full_w, ss_smem ? 1 : 0); break;
         case 1: blend_head_v2_kernel<T, F, CAP, 1><<<grid, kBlend2Threads, smem, st>>>(p, tl, full_h, full_w, ss_smem ? 1 : 0); break;
