@@ -127,7 +127,7 @@ int main(int argc, char **argv) {
         CK(cudaMalloc(&g_in_stats, h.size() * 8));
         CK(cudaMemcpy(g_in_stats, h.data(), h.size() * 8, cudaMemcpyHostToDevice));
     }
-    const int dbgs[] = {0, 16, 16 + 64, 16 + 128, 16 + 256};   // 128: transform without shared-memory loads / stores, 256: without arithmetic   // bit 16 (harness only): FUSE variant
+    const int dbgs[] = {0, 16};   // 128: transform without shared-memory loads / stores, 256: without arithmetic   // bit 16 (harness only): FUSE variant
     printf("dbg bits: 1 no stats, 2 no stores, 4 tap 0 only, 8 all halos = tile 0 (L2 hits), 16 FUSE (deferred InstanceNorm on the halo)\n");
     for (const Layer &L : layers) {
         const int kc = L.Cin % 64 == 0 ? 64 : 32;

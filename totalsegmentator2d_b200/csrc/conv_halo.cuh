@@ -137,7 +137,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA2) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
         for (int s = 0; s < p.n_stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); mbar_init(&ready_bar[s], kHaloXformThreads / 32); }      // one elected arrival per transform warp
-        for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], (!FUSE && kSplit) ? 256 : 128); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], (!FUSE && kSplit) ? 8 : 4); }
         mbar_init(w_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -230,7 +230,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 tmem_ld_wait();
                 if (c == kChunks - 1) {
                     tcgen05_fence_before();
-                    mbar_arrive(&tmem_empty[buf]);        // this thread's TMEM reads of the tile are done
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&tmem_empty[buf]);        // this warp's TMEM reads of the tile are done (one arrival per warp)
                 }
                 uint32_t pk[16];
                 epi_chunk<DT>(r, s_bias + col0 + c * 32, pk, tacc1[c], tacc2[c], do_stats && valid);
