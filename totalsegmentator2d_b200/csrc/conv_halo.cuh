@@ -17,25 +17,30 @@
 //              whole persistent loop (loaded once per CTA): per tile only the halo moves.
 //
 // Measured on B200 (tools/probe/mma_rate.cu): one M=128, K=16 tcgen05.mma costs ~45 cycles at N=32 and ~51 at N=64
-// (the N/2-cycle floor only shows from N=128 on), so these layers are bound by the NUMBER of MMAs (9 taps x Cin/16
-// per tile); everything else - TMA, the operand transform, the epilogue - must stay off that critical path.
+// (the N/2-cycle floor only shows from N=128 on): the A operand is read from shared memory at 128 B/clk (4 KB per instruction = 32
+// cycles), so these layers are bound by the NUMBER of MMAs (9 taps x Cin/16 per tile); everything else - TMA, the operand transform,
+// the epilogue - must stay off that critical path.
 //
 // Deferred normalisation (FUSE): the input is the PRODUCER conv's raw output; its InstanceNorm + LeakyReLU are applied
 // to the halo in shared memory between the TMA arrival and the MMAs (y = leaky(x*scale[n][c] + shift[n][c]), zeros
 // outside the image stay zeros = the conv padding of the normalised tensor), so the normalised tensor is never
-// written to or read from HBM.  Same arithmetic as norm_act_kernel: the two paths are bit-identical.
+// written to or read from HBM.  Same fma / leaky arithmetic as norm_act_kernel (the transformed operand is bit-identical; the
+// fused kernel's own output statistics are summed in a different grouping, see tests/test_gpu_unet.py::test_deferred_norm_matches_materialised).
 //
-// Warp roles (384 threads; see kHaloWarpMma for why in this order): warps 0-7 = 8 EPILOGUE warps, warps 8-9 = halo TRANSFORM warps
-// (FUSE only, idle otherwise), warp 10 TMA producer, warp 11 TMEM alloc + MMA issuer (whole warp convergent, one elected lane issues):
-//   transform (FUSE)  64 threads rewrite every halo stage in place between the TMA arrival (full) and the MMAs (ready): a thread owns
-//                     one 16-byte channel block (its 8 scale / shift pairs live in registers) and walks the halo pixels, loads
-//                     batched before the math; fp32x2 FMA, leaky = max(y, slope*y).  The roles are decoupled: the first version ran
-//                     the transform on the epilogue warps (transform of tile j, then epilogue of tile j-2) and the MMA warp waited
-//                     for TMEM 43% of the time (profiles/r02b_halo_bench_fuse.txt: 2396 cycles per tile against 1025 unfused,
-//                     1790 with an EMPTY transform).
+// Warp roles.  Plain kernel, 384 threads: warps 0-7 = two EPILOGUE warpgroups, (8-9 idle), warp 10 TMA producer, warp 11 TMEM alloc +
+// MMA issuer (whole warp convergent, one elected lane issues).  FUSE kernel, 512 threads: warps 0-3 = ONE epilogue warpgroup,
+// warps 4-11 = eight TRANSFORM warps, (12-13 idle), warp 14 TMA producer, warp 15 MMA issuer; setmaxnreg per role (168 / 216, 96, 64).
+//   transform (FUSE)  the 256 threads split the pixels of every halo stage and rewrite it in place between the TMA arrival (full) and
+//                     the MMAs (ready): a thread owns one 16-byte channel block (its 8 scale / shift pairs live in registers), loads
+//                     batched before the math; fp32x2 FMA, leaky = max(y, slope*y); one elected arrival per warp.  History
+//                     (profiles/r02b..r02m_halo_bench_fuse.txt): the first version ran the transform on the epilogue warps (transform of
+//                     tile j, then epilogue of tile j-2): the MMA warp waited for TMEM 43% of the time, 2396 cycles per tile against 1025
+//                     unfused, 1790 with an EMPTY transform; generic LD/ST instead of LDS/STS cost 3x; one warp sustains ~0.4
+//                     instructions per cycle on this code (tools/probe/xform_rate.cu), hence eight warps.
 //   epilogue          TMEM -> +bias -> round -> per-thread InstanceNorm partial sums -> 32-byte global stores (statistics from the
-//                     fp32 values, FADD2 / FFMA2: see epi_chunk).  BN == 32: the two warpgroups alternate tiles (group g owns
-//                     TMEM buffer g); BN == 64: both work on every tile, one half of the columns each.
+//                     fp32 values, FADD2 / FFMA2: see epi_chunk).  Plain kernel: BN == 32: the two warpgroups alternate tiles (group g
+//                     owns TMEM buffer g); BN == 64: both work on every tile, one half of the columns each.  FUSE kernel: the one
+//                     warpgroup takes every tile and all BN / 32 chunks.
 #pragma once
 #include "conv_tc.cuh"
 
@@ -69,14 +74,8 @@ struct ConvHaloParams {
 
 constexpr int kHaloW = 10, kHaloH = 18, kHaloPix = kHaloW * kHaloH;
 constexpr int kHaloWorkers = 256;           // epilogue threads: warps 0-7
-// Warp roles by warp id.  The latency-critical single warps sit on top (the issue arbiter of an SM sub-partition prefers the highest
-// warp id among its eligible warps), the eight epilogue warps, which mostly wait, are warps 0-7 (TMEM lane quarter = warp % 4 as the
-// hardware requires).  Plain kernel: 384 threads = epilogue 0-7, (8-9 idle), TMA producer 10, MMA issuer 11.  FUSE kernel: 512 threads =
-// ONE epilogue warpgroup 0-3, EIGHT transform warps 4-11, (12-13 idle), TMA producer 14, MMA issuer 15.  Why eight: one warp sustains only ~0.4 instructions per cycle
-// on this dependent fp32x2 code (tools/probe/xform_rate.cu: 107 cycles per 40-instruction step, alone on its SM sub-partition and
-// whether or not other warps spin), a 128-byte-per-pixel stage is 45 such steps = 4800 warp-cycles, and the MMAs of a tile need
-// 1000 - 2000 cycles.  Registers: 512 threads start at 128 each; the epilogue warpgroup raises its share to 168 / 216 (setmaxnreg), the
-// transform warpgroups drop to 96, the TMA / MMA warpgroup to 64.
+// Block shapes (see the header).  Tried and found irrelevant on B200: ordering the roles by warp id (the arbiter's preference for high warp
+// ids), parking the waiting warps with try_wait suspend hints or __nanosleep - a spinning neighbour does not slow a working warp.
 template <bool FUSE> constexpr int halo_threads() { return FUSE ? 512 : 384; }
 template <bool FUSE> constexpr int halo_warp_tma() { return halo_threads<FUSE>() / 32 - 2; }
 template <bool FUSE> constexpr int halo_warp_mma() { return halo_threads<FUSE>() / 32 - 1; }
