@@ -85,6 +85,26 @@ int ts2d_normalize(const float *img_dev, int C, int H, int W, int h0, int h1, in
 int ts2d_resample2d(const float *in_dev, int C, int h, int w, float *out_dev, int h2, int w2, int order,
                     double *scratch_dev, ts2d_stream stream);
 
+/* The order-3 resampler for callers that cannot allocate device memory.  NO COUNTERPART IN THE REFERENCE (its resampling
+ * runs in scipy on the host and allocates freely); it exists for users of this library only.
+ * Who needs it: code that is called back from inside another application's CUDA work and must not call cudaMalloc there
+ * (the call serialises against the whole context and can stall every stream), and bindings that are handed just an input
+ * and an output pointer by their framework and own no device memory pool from which a work area could come.
+ * Same arithmetic and same results as ts2d_resample2d, but the double-precision work area is a fixed array built into
+ * the library: each GPU that loads the library carries it (16 MiB + 512 B) until the process ends.  The call itself
+ * allocates and frees nothing.
+ *   limit   C*(h+24)*(w+24) + 2*C <= ts2d_resample2d_static_capacity() doubles (= 2^21 + 64; two channels of 1000 x 1000
+ *           fit exactly) for order 3; anything larger returns TS2D_ERR_ARG with the sizes in ts2d_last_error().
+ *           Order 1 needs no work area and has no limit.
+ *   sharing every call on a GPU uses the same array: calls that may overlap on the device (two streams, two threads)
+ *           race and produce garbage.  Keep them on one stream, or order them with events.  The array is left dirty
+ *           between calls; each call re-initialises what it needs, so results do not depend on earlier calls.
+ *   set-up  the first call on each GPU (with that GPU current, as for every entry point) asks the runtime for the array's
+ *           device address; issue that first call outside of any stream capture. */
+int ts2d_resample2d_static(const float *in_dev, int C, int h, int w, float *out_dev, int h2, int w2, int order,
+                           ts2d_stream stream);
+int64_t ts2d_resample2d_static_capacity(void);
+
 /* ---- sliding-window tiling ---------------------------------------------------------------
  * Replaces pad_nd_image + slicers + torch.flip in nnUNetPredictor.predict_sliding_window_return_logits
  * (reached from prediction_worker.py:209).  Writes NHWC tiles [T*M][Ph][Pw][C] in `precision`;

@@ -65,6 +65,8 @@ _PROTOS = {
     "ts2d_channel_stats": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
     "ts2d_normalize": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _ip, C.POINTER(C.c_float), _vp, _vp, _vp]),
     "ts2d_resample2d": (_i, [_vp, _i, _i, _i, _vp, _i, _i, _i, _vp, _vp]),
+    "ts2d_resample2d_static": (_i, [_vp, _i, _i, _i, _vp, _i, _i, _i, _vp]),
+    "ts2d_resample2d_static_capacity": (_i64, []),
     "ts2d_extract_tiles": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _ip, _i, _i, _i, _vp, _vp]),
     "ts2d_unet_create": (_i, [C.POINTER(UNetPlan), C.POINTER(_vp)]),
     "ts2d_unet_set_weight": (_i, [_vp, C.c_char_p, _vp, _i64]),

@@ -8,6 +8,8 @@
 // All of it is HBM-bound elementwise / small-reduction work on a few MB; statistics are kept in double.
 #include "common.cuh"
 
+#include <mutex>
+
 namespace ts2d {
 
 // ---------------- bbox of OR_c(img[c] != 0) ---------------------------------------------------------------------
@@ -356,6 +358,86 @@ extern "C" int ts2d_extract_tiles(const float *img_dev, int C, int h, int w, int
     } while (0)
     if (T <= 64) TS2D_EXTRACT(64); else TS2D_EXTRACT(kMaxTiles);
 #undef TS2D_EXTRACT
+    TS2D_LAUNCH_CHECK();
+    return TS2D_OK;
+}
+
+// ---------------- ts2d_resample2d_static: the order-3 resampler for callers that cannot allocate ---------------------
+// ts2d_resample2d needs a double-precision work area (the edge-padded copy the spline prefilter runs over in place, plus
+// two doubles per channel for the clip range) and expects the caller to hand it in.  Some callers have no way to get one:
+// a plugin that runs inside a host application's callback where cudaMalloc is forbidden (it takes a context-wide lock and
+// may synchronise the device), code on a stream that is otherwise kept free of allocator traffic, or a binding that only
+// receives an input and an output pointer from its framework and owns no memory pool of its own.  For them the work area
+// lives inside the library image: one fixed array per GPU, reserved by the driver when the library's module is loaded on
+// that GPU and held until the process exits.
+//
+// Consequences a user must know:
+//   - the limit is kStaticScratchDoubles doubles (16 MiB + 512 B): C*(h+24)*(w+24) + 2*C must fit; two channels of a
+//     1000 x 1000 projection fit exactly.  Larger requests are refused (TS2D_ERR_ARG), never truncated;
+//   - every call on a GPU uses the SAME array.  Two calls that can overlap on the device (different streams, or
+//     different host threads on different streams) corrupt each other; put them on one stream or order them with events;
+//   - the array keeps what the last call left in it.  Nothing here relies on old contents: the clip range is re-initialised
+//     and the padded image is rewritten in full by every call before anything reads it;
+//   - the first call on each GPU looks up the array's device address (cudaGetSymbolAddress, below).  That lookup may load
+//     the module on that GPU, so make the first call per GPU outside of any stream capture; later calls only launch kernels.
+constexpr long long kStaticScratchDoubles = (1ll << 21) + 64;
+static __device__ __align__(256) double g_resample_scratch[kStaticScratchDoubles];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_scratch_mutex;
+double *g_scratch_addr[kMaxDevices] = {};   // per GPU: device address of g_resample_scratch, nullptr until looked up
+
+// In host code `g_resample_scratch` is only a handle for the runtime's symbol table, not memory a kernel may touch: the
+// address the GPU sees has to be asked for, per device, with that device current.
+int static_scratch_for_current_device(double **out) {
+    int dev = -1;
+    TS2D_CHECK_CUDA(cudaGetDevice(&dev));
+    TS2D_REQUIRE(dev >= 0 && dev < kMaxDevices, "ts2d_resample2d_static: device ordinal %d outside 0..%d", dev, kMaxDevices - 1);
+    std::lock_guard<std::mutex> lock(g_scratch_mutex);
+    if (g_scratch_addr[dev] == nullptr) {
+        double *p = nullptr;
+        TS2D_CHECK_CUDA(cudaGetSymbolAddress((void **)&p, g_resample_scratch));
+        TS2D_REQUIRE(p != nullptr, "ts2d_resample2d_static: no device address for the built-in work area on device %d", dev);
+        g_scratch_addr[dev] = p;
+    }
+    *out = g_scratch_addr[dev];
+    return TS2D_OK;
+}
+}  // namespace
+
+extern "C" int64_t ts2d_resample2d_static_capacity(void) { return kStaticScratchDoubles; }
+
+extern "C" int ts2d_resample2d_static(const float *in_dev, int C, int h, int w, float *out_dev, int h2, int w2, int order, ts2d_stream stream) {
+    TS2D_REQUIRE(in_dev && out_dev && C > 0 && h > 0 && w > 0 && h2 > 0 && w2 > 0, "ts2d_resample2d_static: bad arguments");
+    TS2D_REQUIRE(order == 1 || order == 3, "ts2d_resample2d_static: order must be 1 or 3");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (order == 1) {   // no work area at all: same launch as ts2d_resample2d
+        dim3 grid(grid_for((long long)h2 * w2), C);
+        linear_eval_kernel<<<grid, 256, 0, st>>>(in_dev, h, w, out_dev, h2, w2);
+        TS2D_LAUNCH_CHECK();
+        return TS2D_OK;
+    }
+    TS2D_REQUIRE(C <= 32, "ts2d_resample2d_static: C must be <= 32 for order 3");
+    const int ph = h + 2 * kPad, pw = w + 2 * kPad;
+    const long long need = (long long)C * ph * pw + 2ll * C;
+    TS2D_REQUIRE(need <= kStaticScratchDoubles,
+                 "ts2d_resample2d_static: C=%d, %d x %d needs %lld doubles of work area, the built-in one holds %lld "
+                 "(C*(h+24)*(w+24)+2*C must not exceed it); use ts2d_resample2d with caller-owned scratch_dev for larger images",
+                 C, h, w, need, kStaticScratchDoubles);
+    double *scratch = nullptr;
+    const int rc = static_scratch_for_current_device(&scratch);
+    if (rc != TS2D_OK) return rc;
+    double *minmax = scratch + (long long)C * ph * pw;
+    minmax_init_kernel<<<1, 32, 0, st>>>(minmax, C);   // the clip range is the only part that must not carry over
+    TS2D_LAUNCH_CHECK();
+    pad_edge_kernel<<<dim3(grid_for((long long)ph * pw), C), 256, 0, st>>>(in_dev, h, w, scratch, minmax);   // rewrites all C*ph*pw
+    TS2D_LAUNCH_CHECK();
+    spline_prefilter_kernel<<<dim3(ceil_div(pw, 128), C), 128, 0, st>>>(scratch, pw, ph, 1, pw, (long long)ph * pw);
+    TS2D_LAUNCH_CHECK();
+    spline_prefilter_kernel<<<dim3(ceil_div(ph, 128), C), 128, 0, st>>>(scratch, ph, pw, pw, 1, (long long)ph * pw);
+    TS2D_LAUNCH_CHECK();
+    spline_eval3_kernel<<<dim3(grid_for((long long)h2 * w2), C), 256, 0, st>>>(scratch, h, w, out_dev, h2, w2, minmax);
     TS2D_LAUNCH_CHECK();
     return TS2D_OK;
 }
