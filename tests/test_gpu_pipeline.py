@@ -160,6 +160,50 @@ def test_predict_batch_pipeline_equals_predict(zoo):
                 assert np.array_equal(np.asarray(a.get_projection(k).array), np.asarray(b.get_projection(k).array))
 
 
+def test_upload_buffer_memory_outlives_its_wrapper(zoo):
+    """the documented ingest pattern `Image(buf.array, ...)` in a generator that rebinds `buf` per study: the page-locked memory
+    belongs to the array (and to Result['input'], which keeps the Image), not to the UploadBuffer wrapper - dropping the wrapper
+    before the results are consumed must neither free the memory under an upload in flight nor under the returned input image"""
+    import gc
+    from totalsegmentator2d_b200 import ops
+    from totalsegmentator2d_b200.image import Image
+    from totalsegmentator2d_b200.tool import TS2D
+    root, groups = zoo
+    vols = [synthetic_ct(shape, seed=80 + i) for i, shape in enumerate([(90, 20, 70), (110, 24, 64), (70, 16, 100)])]
+    finalizers = []
+
+    def feed():
+        for v in vols:
+            buf = ops.UploadBuffer(v.shape, v.dtype)
+            buf.array[...] = v
+            finalizers.append(buf._finalizer)
+            img = Image(buf.array, (1.5, 1.5, 1.5), (0.0, 0.0, 0.0), np.eye(3).reshape(-1))
+            del buf                       # the wrapper is gone before the upload has even been issued
+            gc.collect()
+            yield img
+
+    with TS2D(key="ts2d", models_root=root, param={"b200.precision": "bf16"}) as ts:
+        want = [np.asarray(ts.predict(Image(v, (1.5, 1.5, 1.5), (0.0, 0.0, 0.0), np.eye(3).reshape(-1))).get_segmentation().array) for v in vols]
+        results = list(ts.predict_batch(feed(), depth=2))
+        gc.collect()
+        assert all(f.alive for f in finalizers)          # every Result still holds its input image
+        for v, r, w in zip(vols, results, want):
+            assert np.array_equal(np.asarray(r.get_input().array).reshape(v.shape), v)
+            assert np.array_equal(np.asarray(r.get_segmentation().array), w)
+    del results, r, ts
+    gc.collect()
+    assert not any(f.alive for f in finalizers)          # ... and the memory goes back once the last holder is gone
+
+    buf = ops.UploadBuffer((4, 8), np.int16)
+    view = buf.array[1:]
+    buf.close()
+    assert not buf.released
+    view[...] = 7                                         # still valid memory
+    del view
+    gc.collect()
+    assert buf.released
+
+
 def test_merge_present_order_on_device():
     """ts2d_merge_present_order == host permutation with labels present first per model (reference meta.py:280-286)"""
     from totalsegmentator2d_b200 import ops

@@ -131,6 +131,8 @@ extern "C" void *ts2d_host_alloc(size_t bytes, int write_combined) {
 }
 extern "C" int ts2d_host_free(void *p) {
     if (!p) return TS2D_OK;
+    cudaDeviceSynchronize();   // an asynchronous upload out of this memory may still be in flight (result deliberately ignored: at exit
+                               // the context may be gone; cudaFreeHost below reports what matters)
     TS2D_CHECK_CUDA(cudaFreeHost(p));
     return TS2D_OK;
 }

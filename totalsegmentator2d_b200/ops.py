@@ -146,32 +146,43 @@ def merge_present_order(src: torch.Tensor, present: torch.Tensor, offsets: Seque
     return out, perm
 
 
+def _release_upload_memory(lib, ptr):
+    try:
+        lib.ts2d_host_free(ptr)
+    except Exception:          # interpreter shutdown: the driver reclaims page-locked memory with the process
+        pass
+
+
 class UploadBuffer:
     """Page-locked (optionally write-combined) host array for a volume that is decoded once and uploaded once:
     ``buf = UploadBuffer((1000, 512, 512), np.int16); buf.array[...] = volume; Image(buf.array, ...)``.  torch recognises the memory as
-    pinned, so ``TS2D.predict`` uploads it with an asynchronous copy.  Keep the object alive while ``array`` is in use."""
+    pinned, so ``TS2D.predict`` uploads it with an asynchronous copy.
+
+    The memory belongs to ``array`` (and to every view, ``Image`` or ``Result['input']`` made from it), not to this wrapper: it is
+    released when the last of them is garbage-collected, so ``buf`` itself may be dropped or rebound at any time - e.g. in a generator that
+    feeds ``TS2D.predict_batch`` and allocates a fresh buffer per study while earlier results are still being consumed.
+    ``ts2d_host_free`` waits for the device before it unpins, so an upload still in flight is not cut short either.
+    ``close()`` only drops this wrapper's own reference."""
 
     def __init__(self, shape, dtype=np.int16, write_combined: bool = True):
         import ctypes
+        import weakref
         lib = L.load(check_device=True)
-        self._lib = lib
         self.nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
-        self._ptr = lib.ts2d_host_alloc(self.nbytes, int(bool(write_combined)))
-        if not self._ptr:
+        ptr = lib.ts2d_host_alloc(self.nbytes, int(bool(write_combined)))
+        if not ptr:
             raise L.TS2DError("ts2d_host_alloc: " + L.last_error())
-        self.array = np.frombuffer((ctypes.c_uint8 * self.nbytes).from_address(self._ptr), dtype=dtype).reshape(shape)
+        owner = (ctypes.c_uint8 * self.nbytes).from_address(ptr)      # the ndarray's base: lives as long as any view of the memory
+        self._finalizer = weakref.finalize(owner, _release_upload_memory, lib, ptr)
+        self.array = np.frombuffer(owner, dtype=dtype).reshape(shape)
+
+    @property
+    def released(self) -> bool:
+        """True once the page-locked memory has gone back to the driver (no array or view of it is left)"""
+        return not self._finalizer.alive
 
     def close(self):
-        if getattr(self, "_ptr", None):
-            self.array = None
-            self._lib.ts2d_host_free(self._ptr)
-            self._ptr = None
-
-    def __del__(self):
-        try:
-            self.close()
-        except Exception:
-            pass
+        self.array = None
 
 
 def pack_mask_bits(mask: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
