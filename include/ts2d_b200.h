@@ -167,6 +167,10 @@ int ts2d_unet_forward_debug(ts2d_unet *u, const void *x_dev, int batch, const ch
  *   zero-fills mask_dev once per study.
  * present_dev (optional): uint8 [ch_total]; element ch_off+c is set to 1 when label c occurs anywhere
  *   (reference ts2d/core/util/meta.py:15-33 get_labels(fetch=True), which decides the merged channel order).
+ * WRITES OUTSIDE THE CROP BOX: when ts2d_unet_blend_covers_image(u) is 1 (fp16 / bf16 plans whose first stage has 8, 16, 32 or 64 features) the call stores this model's
+ *   channels [ch_off, ch_off+heads) of EVERY pixel of the H0 x W0 mask - zeros outside the crop box - so the caller need not clear the
+ *   mask, and a caller that pre-fills or composes those channels itself will find them overwritten.  Channels of other models are never
+ *   touched.  When it returns 0 only the crop box is written and the caller zero-fills mask_dev once per study, as stated above.
  */
 int ts2d_unet_blend_head(ts2d_unet *u, const int *tile_yx_host, int T, int M, int mirror_mask,
                          int pad_top, int pad_left, int h, int w, const float *gaussian_dev,

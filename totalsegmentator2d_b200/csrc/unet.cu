@@ -252,14 +252,27 @@ static int encode_w_map(CUtensorMap *tm, const void *base, int Cin, int Cout, in
     return encode_map(tm, const_cast<void *>(base), 3, dims, str, box, kc, es, is_bf16, promo_w);
 }
 
+// cudaFuncSetAttribute acts on the current device's copy of the kernel, so "already set" has to be remembered per device ordinal (a
+// process may drive several GPUs, and engines may be finalised from several threads): one bit per device in an atomic mask, set only
+// after the calls succeeded.  Two threads that race both make the (idempotent) calls.  Ordinals >= 64 are never cached.
+static inline bool smem_attr_needed(const std::atomic<uint64_t> &mask, int &dev) {
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { dev = -1; return true; }
+    return ((mask.load(std::memory_order_acquire) >> dev) & 1ull) == 0;
+}
+#define TS2D_ONCE_PER_DEVICE(...)                                                           \
+    do {                                                                                    \
+        static std::atomic<uint64_t> _done{0};                                              \
+        int _dev = -1;                                                                      \
+        if (smem_attr_needed(_done, _dev)) {                                                \
+            __VA_ARGS__;                                                                    \
+            if (_dev >= 0) _done.fetch_or(1ull << _dev, std::memory_order_release);         \
+        }                                                                                   \
+    } while (0)
+
 template <int BN, int KC, typename DT>
 static int launch_tc_inst(const CUtensorMap &tmA, const CUtensorMap &tmA2, const CUtensorMap &tmB, const ConvTcParams &p, cudaStream_t st) {
-    static bool attr_set = false;
     constexpr int smem = tc_smem_bytes<BN, KC>();
-    if (!attr_set) {
-        TS2D_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<BN, KC, DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        attr_set = true;
-    }
+    TS2D_ONCE_PER_DEVICE(TS2D_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<BN, KC, DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)));
     const int m_tiles = p.tiles_n * p.tiles_h * p.tiles_w;
     const int total = m_tiles * p.n_tiles_n * std::max(1, p.ksplit);
     if (p.mc) {
@@ -297,12 +310,8 @@ static int launch_tc(int bn, int kc, const CUtensorMap &tmA, const CUtensorMap &
 
 template <int BN, int KC, typename DT>
 static int launch_tc2_inst(const CUtensorMap &tmA, const CUtensorMap &tmA2, const CUtensorMap &tmB, const ConvTcParams &p, cudaStream_t st) {
-    static bool attr_set = false;
     constexpr int smem = tc2_smem_bytes<BN, KC>();
-    if (!attr_set) {
-        TS2D_CHECK_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<BN, KC, DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        attr_set = true;
-    }
+    TS2D_ONCE_PER_DEVICE(TS2D_CHECK_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<BN, KC, DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)));
     const int units = (p.tiles_n * p.tiles_h * p.tiles_w / 2) * p.n_tiles_n;
     const int gx = std::max(1, std::min(units, kNumSMs));
     TS2D_CHECK_CUDA(launch_pdl(conv_tc2_kernel<BN, KC, DT>, dim3(gx), dim3(kTcThreads), smem, st, tmA, tmA2, tmB, p));
@@ -343,11 +352,7 @@ static int halo_smem_bytes(int cin, int bn, int kc, int stages) {
 }
 template <int BN, int KC, typename DT, bool FUSE>
 static int launch_halo_inst(const CUtensorMap &tmA, const CUtensorMap &tmA2, const CUtensorMap &tmB, const ConvHaloParams &p, int smem, cudaStream_t st) {
-    static int attr_smem = 0;
-    if (smem > attr_smem) {
-        TS2D_CHECK_CUDA(cudaFuncSetAttribute(conv_halo_kernel<BN, KC, DT, FUSE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHaloSmemBudget));
-        attr_smem = kHaloSmemBudget;
-    }
+    TS2D_ONCE_PER_DEVICE(TS2D_CHECK_CUDA(cudaFuncSetAttribute(conv_halo_kernel<BN, KC, DT, FUSE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHaloSmemBudget)));
     const int n_tiles_n = p.Cout / BN;
     const int total = p.tiles_x * p.tiles_y * p.N;
     const int gx = std::max(1, std::min(total, kNumSMs / n_tiles_n));
@@ -373,11 +378,7 @@ static int halo_s2_smem_bytes(int cin, int bn, int kc, int stages) {
 }
 template <int BN, int KC, typename DT>
 static int launch_halo_s2_inst(const CUtensorMap &tmA, const CUtensorMap &tmB, const ConvHaloParams &p, int smem, cudaStream_t st) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        TS2D_CHECK_CUDA(cudaFuncSetAttribute(conv_halo_s2_kernel<BN, KC, DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHaloSmemBudget));
-        attr_set = true;
-    }
+    TS2D_ONCE_PER_DEVICE(TS2D_CHECK_CUDA(cudaFuncSetAttribute(conv_halo_s2_kernel<BN, KC, DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHaloSmemBudget)));
     const int n_tiles_n = p.Cout / BN;
     const int total = p.tiles_x * p.tiles_y * p.N;
     const int gx = std::max(1, std::min(total, kNumSMs / n_tiles_n));
@@ -458,11 +459,7 @@ static int launch_first(int cin, const FirstConvParams &p, int N, cudaStream_t s
 }
 template <typename DT>
 static int launch_first_tc(const FirstTcParams &p, cudaStream_t st) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        TS2D_CHECK_CUDA(cudaFuncSetAttribute(conv_first_tc_kernel<DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFtcSmemBytes));
-        attr_set = true;
-    }
+    TS2D_ONCE_PER_DEVICE(TS2D_CHECK_CUDA(cudaFuncSetAttribute(conv_first_tc_kernel<DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFtcSmemBytes)));
     const long long total = (long long)p.tiles_x * p.tiles_y * p.N;
     const int gx = (int)std::max(1LL, std::min(total / 2, (long long)kNumSMs * 2));
     TS2D_CHECK_CUDA(launch_pdl(conv_first_tc_kernel<DT>, dim3(gx, p.Cout / 32), dim3(kFtcThreads), kFtcSmemBytes, st, p));
@@ -1248,14 +1245,12 @@ static int launch_blend2_inst(const BlendParams &p, const int *tile_yx_host, int
     bool ss_smem = p.feat_ss != nullptr;
     size_t smem = blend2_smem_bytes<F>(p.heads, n_img, ss_smem);
     if (smem > 200 * 1024) { ss_smem = false; smem = blend2_smem_bytes<F>(p.heads, n_img, false); }
-    static size_t attr_smem = 48 * 1024;
-    if (smem > attr_smem) {
-        TS2D_CHECK_CUDA(cudaFuncSetAttribute(blend_head_v2_kernel<T, F, CAP, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        TS2D_CHECK_CUDA(cudaFuncSetAttribute(blend_head_v2_kernel<T, F, CAP, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        TS2D_CHECK_CUDA(cudaFuncSetAttribute(blend_head_v2_kernel<T, F, CAP, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        TS2D_CHECK_CUDA(cudaFuncSetAttribute(blend_head_v2_kernel<T, F, CAP, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_smem = 200 * 1024;
-    }
+    if (smem > 48 * 1024)
+        TS2D_ONCE_PER_DEVICE(
+            TS2D_CHECK_CUDA(cudaFuncSetAttribute(blend_head_v2_kernel<T, F, CAP, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            TS2D_CHECK_CUDA(cudaFuncSetAttribute(blend_head_v2_kernel<T, F, CAP, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            TS2D_CHECK_CUDA(cudaFuncSetAttribute(blend_head_v2_kernel<T, F, CAP, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            TS2D_CHECK_CUDA(cudaFuncSetAttribute(blend_head_v2_kernel<T, F, CAP, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)));
     const int full_h = p.mask ? H0 : p.h, full_w = p.mask ? p.W0 : p.w;
     const long long npix = (long long)full_h * full_w;
     TileListT<CAP> tl;
