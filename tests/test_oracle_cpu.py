@@ -280,6 +280,66 @@ def test_nifti_and_metaimage_readers_round_trip(tmp_path):
     assert nrrd.read_nrrd(str(tmp_path / "m.nrrd")).GetMetaData("k") == "a\\nb\nc\\\\"
 
 
+def test_nifti_vector_masks_and_sform_over_qform(tmp_path):
+    """(1) Result.save(ext='nii.gz') writes multi-label masks: vector pixels go out the way ITK writes them (5-D file, dim[5] =
+    components, intent vector) and read back; the nnU-Net export seam honours dataset.json's file_ending through the same dispatcher.
+    (2) a file whose sform and qform disagree is read with the sform when that is a rotation x scale (ITK 5.3+ = SimpleITK 2.5.x, the
+    reference's pin), with the qform when the sform is sheared, and spacing is pixdim."""
+    import struct
+    from totalsegmentator2d_b200 import formats
+    from totalsegmentator2d_b200.core.util.image import read_image
+    from totalsegmentator2d_b200.image import Image
+    rng = np.random.default_rng(9)
+    for shape, sp, org in [((5, 4, 6, 7), (0.7, 1.5, 2.25), (1.0, -2.0, 3.0)), ((4, 6, 3), (1.5, 2.0), (0.5, 1.0))]:
+        v = (rng.random(shape) > 0.5).astype(np.uint8)
+        vi = Image(v, sp, org, None, is_vector=True)
+        for ext in ("nii", "nii.gz"):
+            fp = str(tmp_path / f"vec{len(shape)}.{ext}")
+            formats.write_any(vi, fp)
+            raw = formats.gzip.open(fp, "rb").read() if ext.endswith("gz") else open(fp, "rb").read()
+            dim = struct.unpack("<8h", raw[40:56])
+            assert dim[0] == 5 and dim[4] == 1 and dim[5] == shape[-1] and struct.unpack("<h", raw[68:70])[0] == 1007
+            back = read_image(fp)
+            assert back.is_vector and back.array.dtype == np.uint8
+            assert np.array_equal(np.asarray(back.array).reshape(shape), v)
+            assert np.allclose(back.GetSpacing()[:len(sp)], sp, atol=1e-6) and np.allclose(back.GetOrigin()[:len(org)], org, atol=1e-5)
+    # the dispatcher also serves .nrrd, so export.py can route every file_ending through it
+    formats.write_any(vi, str(tmp_path / "vec.nrrd"))
+    assert np.array_equal(formats.read_any(str(tmp_path / "vec.nrrd")).array, v)
+
+    def nifti(qform_code, sform_code, srow, quat=(0.0, 0.0, 0.0), qoff=(1.0, 2.0, 3.0), pixdim=(1.0, 2.0, 3.0, 4.0)):
+        a = np.arange(2 * 3 * 4, dtype="<i2").reshape(4, 3, 2)
+        hdr = bytearray(352)
+        struct.pack_into("<i", hdr, 0, 348)
+        struct.pack_into("<8h", hdr, 40, 3, 2, 3, 4, 1, 1, 1, 1)
+        struct.pack_into("<2h", hdr, 70, 4, 16)
+        struct.pack_into("<8f", hdr, 76, *pixdim, 0, 0, 0, 0)
+        struct.pack_into("<3f", hdr, 108, 352.0, 1.0, 0.0)
+        struct.pack_into("<2h", hdr, 252, qform_code, sform_code)
+        struct.pack_into("<6f", hdr, 256, *quat, *qoff)
+        struct.pack_into("<12f", hdr, 280, *srow)
+        hdr[344:348] = b"n+1\0"
+        fp = str(tmp_path / f"q{qform_code}s{sform_code}_{abs(hash(tuple(srow))) % 9999}.nii")
+        with open(fp, "wb") as f:
+            f.write(bytes(hdr) + a.tobytes())
+        return fp
+
+    # qform: identity rotation (RAS), offset (1,2,3); sform: 90 degree turn about z with offset (5,6,7) -> the sform must win
+    turned = (0, -3, 0, 5, 2, 0, 0, 6, 0, 0, 4, 7)           # columns: x -> +y (2 mm), y -> -x (3 mm), z -> +z (4 mm)
+    back = read_image(nifti(1, 1, turned))
+    assert np.allclose(back.GetSpacing(), (2, 3, 4))
+    assert np.allclose(back.GetOrigin(), (-5, -6, 7))
+    assert np.allclose(back.direction_matrix(), np.diag([-1.0, -1.0, 1.0]) @ np.array([[0, -1, 0], [1, 0, 0], [0, 0, 1.0]]))
+    # the same file with a sheared sform: not a rotation x scale, so the qform (identity, offset (1,2,3)) is used
+    sheared = (2, 1.5, 0, 5, 0, 3, 0, 6, 0, 0, 4, 7)
+    back = read_image(nifti(1, 1, sheared))
+    assert np.allclose(back.GetOrigin(), (-1, -2, 3)) and np.allclose(back.direction_matrix(), np.diag([-1.0, -1.0, 1.0]))
+    assert np.allclose(back.GetSpacing(), (2, 3, 4))
+    # qform only / sform only keep working
+    assert np.allclose(read_image(nifti(1, 0, turned)).GetOrigin(), (-1, -2, 3))
+    assert np.allclose(read_image(nifti(0, 2, turned)).GetOrigin(), (-5, -6, 7))
+
+
 def test_visual_restatement_properties():
     """oracle/visual.py (create_visual restatement): identity geometry is the identity, label = highest non-zero component,
     background black, 2x finer uniform grid replicates pixels around the kept centre index, window endpoints map to 0 / 255."""

@@ -26,7 +26,6 @@ import torch
 from ... import _lib as L
 from ... import ops
 from ...image import Image
-from ...nrrd import write_nrrd
 from .plans import foreground_labels, read_json
 
 
@@ -91,4 +90,6 @@ def export_prediction_from_logits(predicted_array_or_file: Union[np.ndarray, tor
             raise RuntimeError("cannot restore the 3-D container shape of the input image")
         arr = arr.reshape(shape + [arr.shape[-1]])
     img = Image(arr, sp, org, dr, is_vector=True)
-    write_nrrd(img, output_file_truncated + dj["file_ending"], True)
+    # dataset.json's file_ending names the container (upstream: the reader/writer class is chosen by it): .nrrd, .nii(.gz), .mha/.mhd
+    from ...formats import write_any
+    write_any(img, output_file_truncated + dj["file_ending"])

@@ -42,6 +42,15 @@ def _quat_to_mat(b: float, c: float, d: float, qfac: float) -> np.ndarray:
     return R
 
 
+def _sform_is_unsheared(M: np.ndarray, tol: float = 1e-3) -> bool:
+    """True when the 3x3 part of an sform is rotation x per-axis scale: its normalised columns are mutually orthogonal"""
+    n = np.linalg.norm(M, axis=0)
+    if np.any(n < 1e-12) or not np.all(np.isfinite(M)):
+        return False
+    Q = M / n[None, :]
+    return bool(np.abs(Q.T @ Q - np.eye(3)).max() < tol)
+
+
 def read_nifti(path: str) -> Image:
     with open(path, "rb") as f:
         buf = f.read()
@@ -94,30 +103,39 @@ def read_nifti(path: str) -> Image:
     arr = np.ascontiguousarray(arr.astype(dt.newbyteorder("="), copy=False))
     if slope != 0.0 and not (slope == 1.0 and inter == 0.0) and np.isfinite(slope) and np.isfinite(inter):
         arr = (arr.astype(np.float64) * float(slope) + float(inter)).astype(np.float32)
-    # affine voxel -> RAS mm
+    # affine voxel -> RAS mm.  Which transform wins when both are present follows ITK 5.3+ (SimpleITK 2.5.x, the reference's pin in
+    # pyproject.toml): an sform with sform_code > 0 whose 3x3 part is a rotation times a per-axis scale (no shear) is preferred,
+    # otherwise the qform, otherwise pixdim alone.  ITK 4 preferred the qform.  Spacing is pixdim (as ITK reads it) when positive.
+    pd = np.array([abs(pixdim[1]) or 1.0, abs(pixdim[2]) or 1.0, abs(pixdim[3]) or 1.0])
     A = np.eye(4)
-    if qform_code > 0:
+    if sform_code > 0 and _sform_is_unsheared(srow[:, :3]):
+        A[:3, :] = srow
+    elif qform_code > 0:
         qfac = -1.0 if pixdim[0] < 0 else 1.0
         R = _quat_to_mat(qb, qc, qd, qfac)
-        A[:3, :3] = R * np.array([abs(pixdim[1]) or 1.0, abs(pixdim[2]) or 1.0, abs(pixdim[3]) or 1.0])[None, :]
+        A[:3, :3] = R * pd[None, :]
         A[:3, 3] = [qx, qy, qz]
     elif sform_code > 0:
         A[:3, :] = srow
     else:
-        A[:3, :3] = np.diag([abs(pixdim[1]) or 1.0, abs(pixdim[2]) or 1.0, abs(pixdim[3]) or 1.0])
+        A[:3, :3] = np.diag(pd)
     A = np.diag([-1.0, -1.0, 1.0, 1.0]) @ A            # RAS -> LPS
     M = A[:3, :3]
-    spacing = np.linalg.norm(M, axis=0)
-    spacing[spacing == 0] = 1.0
-    D = M / spacing[None, :]
+    norms = np.linalg.norm(M, axis=0)
+    norms[norms == 0] = 1.0
+    D = M / norms[None, :]
+    spacing = np.where(np.array(pixdim[1:4]) > 0, pd, norms)
     return Image(arr, tuple(spacing[:sd]), tuple(A[:sd, 3]), D[:sd, :sd].reshape(-1), is_vector=ncomp > 1)
 
 
 def write_nifti(img: Image, path: str) -> None:
     """NIfTI-1 single file (n+1), qform and sform both set; gzip when the name ends in .gz."""
     arr = np.asarray(img.array)
+    ncomp = 1
     if img.is_vector:
-        raise RuntimeError("vector images are written as .nrrd (NIfTI export of multi-component masks is not implemented)")
+        # ITK's layout for vector pixels: a 5-D file, dim = (5, nx, ny, nz, 1, C), intent NIFTI_INTENT_VECTOR, component slowest
+        ncomp = int(arr.shape[-1])
+        arr = np.ascontiguousarray(np.moveaxis(arr, -1, 0))
     code = arr.dtype.str[1:]
     if code not in _NIFTI_CODES:
         raise RuntimeError(f"unsupported pixel type {arr.dtype} for NIfTI")
@@ -153,9 +171,13 @@ def write_nifti(img: Image, path: str) -> None:
             b, c, d = -b, -c, -d
     hdr = bytearray(352)
     struct.pack_into("<i", hdr, 0, 348)
-    struct.pack_into("<8h", hdr, 40, 3, size[0], size[1], size[2], 1, 1, 1, 1)
+    if ncomp > 1:
+        struct.pack_into("<8h", hdr, 40, 5, size[0], size[1], size[2], 1, ncomp, 1, 1)
+        struct.pack_into("<h", hdr, 68, 1007)           # intent_code = NIFTI_INTENT_VECTOR
+    else:
+        struct.pack_into("<8h", hdr, 40, 3, size[0], size[1], size[2], 1, 1, 1, 1)
     struct.pack_into("<2h", hdr, 70, _NIFTI_CODES[code], arr.dtype.itemsize * 8)
-    struct.pack_into("<8f", hdr, 76, qfac, sp[0], sp[1], sp[2], 0, 0, 0, 0)
+    struct.pack_into("<8f", hdr, 76, qfac, sp[0], sp[1], sp[2], 0, 1.0 if ncomp > 1 else 0, 0, 0)
     struct.pack_into("<3f", hdr, 108, 352.0, 1.0, 0.0)
     hdr[123] = 2                                        # xyzt_units: millimetres
     struct.pack_into("<2h", hdr, 252, 1, 1)
@@ -274,6 +296,9 @@ def read_any(path: str) -> Image:
         return read_nifti(path)
     if low.endswith(".mha") or low.endswith(".mhd"):
         return read_metaimage(path)
+    if low.endswith(".nrrd") or low.endswith(".nhdr"):
+        from .nrrd import read_nrrd
+        return read_nrrd(path)
     raise RuntimeError(f"unsupported image format: {path}")
 
 
@@ -283,4 +308,7 @@ def write_any(img: Image, path: str) -> None:
         return write_nifti(img, path)
     if low.endswith(".mha") or low.endswith(".mhd"):
         return write_metaimage(img, path, True)
+    if low.endswith(".nrrd"):
+        from .nrrd import write_nrrd
+        return write_nrrd(img, path, True)
     raise RuntimeError(f"unsupported image format: {path}")
