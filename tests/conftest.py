@@ -52,3 +52,16 @@ def cs512_zoo(tmp_path_factory):
 def oracle_models(root, model_key, groups):
     from oracle import pipeline as opipe
     return {f"{model_key}_{g}": opipe.OracleModel(opipe.find_training_dir(os.path.join(root, f"{model_key}_{g}", "r001"))) for g in groups}
+
+
+@pytest.fixture(scope="session")
+def cs512_trained_zoo(tmp_path_factory):
+    """the same five CS-512 group models with TRAINED-LIKE weights (tools/make_trained_like_zoo.py: a few hundred Adam steps on
+    synthetic projections with organ-like targets, ~10 s per model on the GPU box), written once per session; the north_star gates
+    (99.9 % masks, 1e-2 logits) are asserted on this zoo"""
+    import bench
+    from tools import make_trained_like_zoo as mk
+    from totalsegmentator2d_b200 import synth
+    root = str(tmp_path_factory.mktemp("cs512_trained_zoo"))
+    mk.write_trained_like_zoo(root, bench.MODEL_KEY, synth.TS2D_V2_GROUPS, synth.cs512_arch(), steps=int(os.environ.get("TS2D_TRAIN_STEPS", "400")))
+    return root, synth.TS2D_V2_GROUPS

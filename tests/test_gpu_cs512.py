@@ -16,7 +16,9 @@ error by ~1.25 x per layer (fp32 round-off, 6e-8, reaches ~1e-5 at the logits th
 (a) MEASURE the reference arithmetic on the same GPU - ``oracle.nnunet_net.unet_forward`` (F.conv2d / F.instance_norm /
 F.leaky_relu / F.conv_transpose2d, what PlainConvUNet executes) under ``torch.autocast('cuda', float16)`` - against the same
 fp32 oracle, (b) require this engine to be AT LEAST AS CLOSE to the fp32 oracle as that (REL_GATE), and (c) keep the literal
-north_star gates as ``xfail`` tests that print the measured numbers, so the gap stays visible in every test report.
+north_star gates as ``xfail`` tests that print the measured numbers, so the gap stays visible in every test report.  The gates
+themselves are asserted, without xfail, on the trained-like zoo in tests/test_gpu_trained_like.py; the runs here are the random-init
+diagnostics.
 Reference semantics: ts2d/core/inference/prediction_worker.py:206-221, ts2d/core/inference/wrapper.py:65-66.
 """
 import os
@@ -33,7 +35,7 @@ pytestmark = pytest.mark.gpu
 LOGIT_GATE = 1e-2        # north_star: "logits: within 1e-2 absolute in bf16" (reduced-precision path)
 LOGIT_GATE_F32 = 1e-4    # north_star: "1e-4 in fp32"
 MASK_GATE = 0.999        # north_star: "thresholded label masks: at least 99.9% pixel agreement"
-REL_GATE = 1.10          # this engine's mean |logit error| vs the fp32 oracle <= REL_GATE x the reference arithmetic's (torch fp16 autocast)
+REL_GATE = 1.00          # this engine's mean |logit error| vs the fp32 oracle <= REL_GATE x the reference arithmetic's (torch fp16 autocast)
 MASK_FLOOR = 0.995       # fp16-operand arithmetic on random-init CS-512 (reference arithmetic measured: ~0.996-0.998, printed per test)
 NORTH_STAR_XFAIL = ("16-bit-operand arithmetic cannot meet the north_star gate on random-init CS-512; the reference's own fp16-autocast "
                     "arithmetic misses it by the same margin (see test_cs512_engine_is_as_close_as_reference_fp16_autocast)")
