@@ -179,6 +179,36 @@ def test_combine_order_absent_labels_follow_std_map_key_order():
     assert np.array_equal(np.asarray(out.array), merged)
 
 
+def test_orientation_remap_against_hand_derived_vectors():
+    """sitk.DICOMOrient(img, 'RAI') (reference ts2d/core/util/image.py:32-43) as literal expectations worked out by hand, so that the
+    product's host logic and the oracle are not only checked against each other.  DICOMOrient letters say where an axis points TO in
+    LPS (+x = L, +y = P, +z = S); column r of the direction matrix is where image axis r points.
+      diag(-1,-1,+1) (the reference's sample_s0521): x -> R, y -> A already; z -> S must become I: z flip only
+      identity (LPS): all three axes reversed
+      columns (+y, -x, -z): R is image axis 1 as it is, A is axis 0 reversed (it points P), I is axis 2 as it is
+      columns (+x, +z, -y): R is axis 0 reversed, A is axis 2 as it is, I is axis 1 reversed
+      diag(-1,-1,-1) turned 0.3 rad about z (oblique): the dominant cosines decide: nothing to do"""
+    from oracle import geometry
+    from totalsegmentator2d_b200.core.util.image import orientation_remap
+    th = 0.3
+    rot = np.array([[np.cos(th), -np.sin(th), 0], [np.sin(th), np.cos(th), 0], [0, 0, 1.0]])
+    cases = [
+        (np.diag([-1.0, -1.0, 1.0]), (0, 1, 2), (False, False, True)),
+        (np.eye(3), (0, 1, 2), (True, True, True)),
+        (np.array([[0.0, -1.0, 0.0], [1.0, 0.0, 0.0], [0.0, 0.0, -1.0]]), (1, 0, 2), (False, True, False)),
+        (np.array([[1.0, 0.0, 0.0], [0.0, 0.0, -1.0], [0.0, 1.0, 0.0]]), (0, 2, 1), (True, False, True)),
+        (rot @ np.diag([-1.0, -1.0, -1.0]), (0, 1, 2), (False, False, False)),
+    ]
+    for D, perm, flip in cases:
+        for fn in (orientation_remap, geometry.orientation_remap):
+            got = fn(D * 1.5 if fn is orientation_remap else D, "RAI")       # a spacing factor on the matrix must not matter to the product's rule
+            assert (tuple(got[0]), tuple(bool(f) for f in got[1])) == (perm, flip), (fn.__module__, D.tolist(), got)
+    # the same rule read the other way: for target 'LPS' every flip is the opposite one
+    for D, perm, flip in cases:
+        got = orientation_remap(D, "LPS")
+        assert tuple(got[0]) == perm and tuple(bool(f) for f in got[1]) == tuple(not f for f in flip)
+
+
 def test_default_compute_type_is_the_references_autocast_type():
     """fp16 (what nnU-Net's autocast computes in on CUDA) is the default storage type of the engine, the bench and the tools: it is the
     16-bit type that meets the 99.9 % mask gate against the fp32 oracle (bf16: 0.9939 on random-init weights, tests/test_gpu_pipeline.py)"""
