@@ -204,6 +204,11 @@ int ts2d_unpack_mask_bits_host(const uint8_t *packed_host, uint8_t *out_host, in
  * GPU over PCIe without cache snoops). Returns NULL on failure (ts2d_last_error). */
 void *ts2d_host_alloc(size_t bytes, int write_combined);
 int ts2d_host_free(void *ptr);
+/* Upload of a volume held in ordinary (pageable) host memory - what sitk.ReadImage returns (ts2d/core/util/image.py:225-238) - at close to
+ * page-locked speed: the library stages it through its own ring of page-locked slots (4 x 32 MiB per GPU, allocated at the first call on that
+ * GPU and kept), `threads` CPU threads filling slot i+1 while slot i is in flight.  Returns once src_host has been read completely; the
+ * device copy completes in stream order.  One staged upload runs at a time per process. */
+int ts2d_upload_pageable(void *dst_dev, const void *src_host, size_t bytes, int threads, ts2d_stream stream);
 /* re-allocates the workspace for a larger/smaller max_batch (weights are kept) */
 int ts2d_unet_resize(ts2d_unet *u, int max_batch);
 /* number of kernel launches this engine issued since creation (bench.py's gpu_launches) */

@@ -204,6 +204,33 @@ def test_upload_buffer_memory_outlives_its_wrapper(zoo):
     assert buf.released
 
 
+def test_staged_upload_of_pageable_volumes():
+    """ts2d_upload_pageable (ring of page-locked slots filled by several CPU threads) == a plain copy, for sizes that wrap the 4 x 32 MiB
+    ring, an odd tail, two uploads back to back on different streams, a read-only source, and through the product path
+    (core.util.image._to_device picks it for pageable arrays >= 16 MiB; uint16 goes through its int16 view)"""
+    from totalsegmentator2d_b200 import _lib as L
+    from totalsegmentator2d_b200.core.util.image import _to_device
+    lib = L.load(check_device=True)
+    rng = np.random.default_rng(17)
+    a = rng.integers(0, 255, size=(5 * 32 << 20) + 12345, dtype=np.uint8)      # 5 chunks + tail: slot 0 is reused
+    b = rng.integers(0, 255, size=(40 << 20) + 1, dtype=np.uint8)
+    da = torch.empty(a.size, dtype=torch.uint8, device="cuda")
+    db = torch.empty(b.size, dtype=torch.uint8, device="cuda")
+    s2 = torch.cuda.Stream()
+    L.check(lib.ts2d_upload_pageable(da.data_ptr(), a.ctypes.data, a.nbytes, 4, L.stream_ptr()), "ts2d_upload_pageable")
+    L.check(lib.ts2d_upload_pageable(db.data_ptr(), b.ctypes.data, b.nbytes, 1, L.stream_ptr(s2)), "ts2d_upload_pageable")
+    torch.cuda.synchronize()
+    assert np.array_equal(da.cpu().numpy(), a) and np.array_equal(db.cpu().numpy(), b)
+    vol = rng.integers(-1024, 3071, size=(300, 200, 256), dtype=np.int16)       # 30.7 MB: above the staging threshold
+    vol.flags.writeable = False
+    assert np.array_equal(_to_device(vol).cpu().numpy(), vol)
+    u16 = rng.integers(0, 65535, size=(300, 200, 256), dtype=np.uint16)
+    got = _to_device(u16)
+    assert got.dtype == torch.uint16 and np.array_equal(got.view(torch.int16).cpu().numpy().view(np.uint16), u16)
+    small = rng.integers(-5, 5, size=(10, 20, 30), dtype=np.int16)              # below the threshold: plain copy
+    assert np.array_equal(_to_device(small).cpu().numpy(), small)
+
+
 def test_merge_present_order_on_device():
     """ts2d_merge_present_order == host permutation with labels present first per model (reference meta.py:280-286)"""
     from totalsegmentator2d_b200 import ops

@@ -86,6 +86,7 @@ _PROTOS = {
     "ts2d_pack_mask_bits": (_i, [_vp, _vp, _i64, _vp]),
     "ts2d_host_alloc": (_vp, [C.c_size_t, _i]),
     "ts2d_host_free": (_i, [_vp]),
+    "ts2d_upload_pageable": (_i, [_vp, _vp, C.c_size_t, _i, _vp]),
     "ts2d_unpack_mask_bits_host": (_i, [_vp, _vp, _i64, _i]),
     "ts2d_unet_direct_layer_count": (_i, [_vp]),
     "ts2d_unet_check_guards": (_i, [_vp]),

@@ -73,9 +73,32 @@ def _to_device(arr: np.ndarray) -> torch.Tensor:
     if isinstance(arr, torch.Tensor):
         return arr.cuda(non_blocking=True).contiguous()
     a = np.ascontiguousarray(arr)
-    if a.dtype == np.uint16:
-        return torch.from_numpy(a.view(np.int16)).cuda(non_blocking=True).view(torch.uint16)
-    return torch.from_numpy(a).cuda(non_blocking=True)      # asynchronous when the array lives in pinned memory
+    view = a.view(np.int16) if a.dtype == np.uint16 else a
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore", UserWarning)          # read-only arrays (np.frombuffer of a decoded file): the upload never writes
+        src = torch.from_numpy(view)
+    if view.nbytes >= _STAGED_UPLOAD_MIN_BYTES and not src.is_pinned():
+        # pageable memory (what read_image returns): staged through the library's page-locked ring by several CPU threads
+        lib = L.load()
+        dst = torch.empty(src.shape, dtype=src.dtype, device="cuda")
+        L.check(lib.ts2d_upload_pageable(dst.data_ptr(), view.ctypes.data, view.nbytes, _upload_threads(), L.stream_ptr()), "ts2d_upload_pageable")
+    else:
+        dst = src.cuda(non_blocking=True)                     # asynchronous when the array lives in pinned memory
+    return dst.view(torch.uint16) if a.dtype == np.uint16 else dst
+
+
+_STAGED_UPLOAD_MIN_BYTES = 16 << 20
+
+
+def _upload_threads() -> int:
+    """CPU threads of the staged upload: $TS2D_UPLOAD_THREADS, else 8 shared between the ranks on this host"""
+    import os
+    env = os.environ.get("TS2D_UPLOAD_THREADS")
+    if env:
+        return max(1, int(env))
+    world = max(1, int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("WORLD_SIZE", "1"))))
+    return max(1, min(8, (os.cpu_count() or 8) // world))
 
 
 def reorient_image(img: Image, orient: str = "RAI") -> Image:
